@@ -1,0 +1,163 @@
+"""ctypes loader for the CPU oracle (oracle/libnerf_oracle.so) and, in the dev container, the host build of the
+reference's own kernels (oracle/_ref/libnerf_ref.so).
+
+TEST INFRASTRUCTURE: importable only from tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs.  The product package never imports this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+_u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+_u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+
+
+def build(ref=True):
+    subprocess.run(["make", "-s", "-C", HERE, "libnerf_oracle.so"], check=True)
+    if ref and os.path.isdir("/root/reference/include/nerf-cuda"):
+        subprocess.run([os.path.join(HERE, "build_ref.sh")], check=True, stdout=subprocess.DEVNULL)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(HERE, "libnerf_oracle.so")
+        if not os.path.exists(path):
+            build(ref=False)
+        _lib = C.CDLL(path)
+        _lib.orc_march.restype = C.c_longlong
+        _lib.orc_render_frame.restype = C.c_longlong
+    return _lib
+
+
+def _p(a, ty):
+    return a.ctypes.data_as(C.POINTER(ty)) if a is not None else None
+
+
+class Oracle:
+    """Holds a model (fp16 weights + table, float grid) and exposes each stage of the hot path."""
+
+    def __init__(self, desc, params_f32, grid, aabb):
+        self.l = lib()
+        self.desc = desc
+        self.grid = np.ascontiguousarray(grid, np.float32)
+        self.aabb = np.ascontiguousarray(aabb, np.float32)
+        p16 = np.empty(params_f32.size, np.uint16)
+        self.l.orc_cast_f16(_p(np.ascontiguousarray(params_f32, np.float32), C.c_float), _p(p16, C.c_uint16),
+                            C.c_size_t(params_f32.size))
+        self.mlp = np.ascontiguousarray(p16[:10240])
+        self.table = np.ascontiguousarray(p16[10240:])
+
+    def level_table(self):
+        L = self.desc.n_levels
+        offs, sc, res = np.zeros(L + 1, np.uint32), np.zeros(L, np.float32), np.zeros(L, np.uint32)
+        pls = C.c_float()
+        rc = self.l.orc_level_table(C.byref(self.desc), _p(offs, C.c_uint32), _p(sc, C.c_float), _p(res, C.c_uint32),
+                                    C.byref(pls))
+        assert rc == 0
+        return offs, sc, res, pls.value
+
+    def rays(self, intr, pose, W, H, pix0=0, n=None):
+        n = W * H - pix0 if n is None else n
+        o, d = np.zeros(3, np.float32), np.zeros((n, 3), np.float32)
+        nr, fr = np.zeros(n, np.float32), np.zeros(n, np.float32)
+        self.l.orc_rays(C.byref(self.desc), _p(self.aabb, C.c_float), _p(intr, C.c_float), _p(pose, C.c_float), W, H,
+                        pix0, n, _p(o, C.c_float), _p(d, C.c_float), _p(nr, C.c_float), _p(fr, C.c_float))
+        return o, d, nr, fr
+
+    def march(self, o, d, nears, fars, want_samples=True):
+        n = d.shape[0]
+        counts = np.zeros(n, np.int32)
+        args = (C.byref(self.desc), _p(self.grid, C.c_float), n, _p(o, C.c_float), _p(d, C.c_float),
+                _p(nears, C.c_float), _p(fars, C.c_float), _p(counts, C.c_int32))
+        total = self.l.orc_march(*args, None, C.c_size_t(0))
+        if not want_samples:
+            return counts, None
+        samples = np.zeros((max(total, 1), 8), np.float32)
+        got = self.l.orc_march(*args, _p(samples, C.c_float), C.c_size_t(samples.shape[0]))
+        assert got == total
+        return counts, samples[:total]
+
+    def encode(self, positions, want_indices=False):
+        n = positions.shape[0]
+        enc = np.zeros((n, 32), np.uint16)
+        idx = np.zeros((n, self.desc.n_levels, 8), np.uint32) if want_indices else None
+        rc = self.l.orc_encode(C.byref(self.desc), _p(self.table, C.c_uint16), n,
+                               _p(np.ascontiguousarray(positions, np.float32), C.c_float), _p(enc, C.c_uint16),
+                               _p(idx, C.c_uint32))
+        assert rc == 0
+        return (enc, idx) if want_indices else enc
+
+    def sh(self, dirs01):
+        n = dirs01.shape[0]
+        out = np.zeros((n, 16), np.uint16)
+        self.l.orc_sh(n, _p(np.ascontiguousarray(dirs01, np.float32), C.c_float), _p(out, C.c_uint16))
+        return out
+
+    def network(self, enc_u16, dirs01):
+        n = enc_u16.shape[0]
+        out = np.zeros((n, 4), np.float32)
+        rc = self.l.orc_network(C.byref(self.desc), _p(self.mlp, C.c_uint16), n,
+                                _p(np.ascontiguousarray(enc_u16, np.uint16), C.c_uint16),
+                                _p(np.ascontiguousarray(dirs01, np.float32), C.c_float), _p(out, C.c_float))
+        assert rc == 0
+        return out
+
+    def samples(self, positions01, dirs01):
+        n = positions01.shape[0]
+        out = np.zeros((n, 4), np.float32)
+        rc = self.l.orc_samples(C.byref(self.desc), _p(self.mlp, C.c_uint16), _p(self.table, C.c_uint16), n,
+                                _p(np.ascontiguousarray(positions01, np.float32), C.c_float),
+                                _p(np.ascontiguousarray(dirs01, np.float32), C.c_float), _p(out, C.c_float))
+        assert rc == 0
+        return out
+
+    def render(self, intr, pose, W, H, pix0=0, npix=None):
+        npix = W * H - pix0 if npix is None else npix
+        rgb, depth = np.zeros((npix, 3), np.float32), np.zeros(npix, np.float32)
+        counts = np.zeros(npix, np.int32)
+        total = self.l.orc_render_frame(C.byref(self.desc), _p(self.mlp, C.c_uint16), _p(self.table, C.c_uint16),
+                                        _p(self.grid, C.c_float), _p(self.aabb, C.c_float), _p(intr, C.c_float),
+                                        _p(pose, C.c_float), W, H, pix0, npix, _p(rgb, C.c_float),
+                                        _p(depth, C.c_float), _p(counts, C.c_int32))
+        assert total >= 0
+        return rgb, depth, counts
+
+    def to_u8(self, img):
+        a = np.ascontiguousarray(img, np.float32)
+        out = np.zeros(a.shape, np.uint8)
+        self.l.orc_to_u8(_p(a, C.c_float), _p(out, C.c_uint8), C.c_size_t(a.size))
+        return out
+
+    def num_threads(self):
+        return self.l.orc_num_threads()
+
+
+def half_to_float(u16):
+    return np.ascontiguousarray(u16, np.uint16).view(np.float16).astype(np.float32)
+
+
+# ---- host build of the reference's own kernels (dev container only) -------------------------------------------------
+_ref = None
+
+
+def ref_available():
+    return os.path.exists(os.path.join(HERE, "_ref", "libnerf_ref.so"))
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        _ref = C.CDLL(os.path.join(HERE, "_ref", "libnerf_ref.so"))
+    return _ref
