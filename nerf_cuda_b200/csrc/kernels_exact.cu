@@ -1,0 +1,258 @@
+// kernels_exact.cu — ray setup, occupancy march (count + emit) and the occupancy bitfield builder.
+//
+// This translation unit is compiled with -fmad=false: every expression below is evaluated exactly as the
+// reference writes it (no FMA contraction, IEEE div/sqrt) so that ray directions, near/far, sample positions,
+// step sizes and sample counts are BIT-EXACT against the oracle (oracle/nerf_oracle.cpp, -ffp-contract=off).
+//
+// Replaces the reference kernels K1-K7 of SURVEY.md §2c:
+//   set_rays_o/set_rays_d (include/nerf-cuda/render_utils.h:31-66), kernel_near_far_from_aabb (:338-392),
+//   init_step0 (:221-239), kernel_compact_rays (:394-415), kernel_march_rays (:524-655),
+//   linear_transformer x2 (include/nerf-cuda/common_device.cuh:31-36), concat_network_in_and_out (:280-306).
+// Design: one pass over whole rays instead of a host-driven <=8-step wavefront with a blocking D2H per iteration
+// (src/nerf_render.cu:269-338).  Pass 1 counts samples per ray and reduces per block; a one-block scan gives block
+// bases; pass 2 re-marches and writes a COMPACT, ray-major sample list (warp-shuffle scan inside the block).
+#include "nrf_device.cuh"
+
+#define RAYS_BLOCK 128
+
+__device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(hi, fmaxf(lo, x)); }
+
+// ---- K1-K5: ray direction + slab test ---------------------------------------------------------------------------
+__device__ __forceinline__ void ray_dir(const MarchParams& P, int p, float d[3]) {
+  const float i = (float)(p % P.W) + 0.5f;
+  const float j = (float)(p / P.W) + 0.5f;
+  const float xs = (i - P.intr[2]) / P.intr[0] * 1.0f;
+  const float ys = (j - P.intr[3]) / P.intr[1] * 1.0f;
+  const float zs = 1.0f;
+  const float nrm = sqrtf(xs * xs + (ys * ys + zs * zs));  // Eigen fixed-size-3 reduction order
+  const float v0 = xs / nrm, v1 = ys / nrm, v2 = zs / nrm;
+#pragma unroll
+  for (int r = 0; r < 3; ++r) d[r] = P.R[r * 3 + 0] * v0 + (P.R[r * 3 + 1] * v1 + P.R[r * 3 + 2] * v2);
+}
+
+__device__ __forceinline__ void near_far(const MarchParams& P, const float d[3], float& near_o, float& far_o) {
+  const float rdx = 1 / d[0], rdy = 1 / d[1], rdz = 1 / d[2];
+  float near = (P.aabb[0] - P.o[0]) * rdx, far = (P.aabb[3] - P.o[0]) * rdx;
+  if (near > far) { float t = near; near = far; far = t; }
+  float near_y = (P.aabb[1] - P.o[1]) * rdy, far_y = (P.aabb[4] - P.o[1]) * rdy;
+  if (near_y > far_y) { float t = near_y; near_y = far_y; far_y = t; }
+  if (near > far_y || near_y > far) { near_o = far_o = 3.402823466e+38f; return; }
+  if (near_y > near) near = near_y;
+  if (far_y < far) far = far_y;
+  float near_z = (P.aabb[2] - P.o[2]) * rdz, far_z = (P.aabb[5] - P.o[2]) * rdz;
+  if (near_z > far_z) { float t = near_z; near_z = far_z; far_z = t; }
+  if (near > far_z || near_z > far) { near_o = far_o = 3.402823466e+38f; return; }
+  if (near_z > near) near = near_z;
+  if (far_z < far) far = far_z;
+  if (near < P.min_near) near = P.min_near;
+  near_o = near;
+  far_o = far;
+}
+
+// ---- K7: one iteration of the march loop (render_utils.h:596-651) ---------------------------------------------------
+struct Step {
+  float x, y, z, dt;
+  uint32_t cell;
+  int level;
+};
+
+__device__ __forceinline__ bool march_step(const MarchParams& P, const float d[3], const float rd[3], float& t,
+                                           Step& s) {
+  const float x = clampf(P.o[0] + t * d[0], -P.bound, P.bound);
+  const float y = clampf(P.o[1] + t * d[1], -P.bound, P.bound);
+  const float z = clampf(P.o[2] + t * d[2], -P.bound, P.bound);
+  // mip_from_pos: frexpf exponent of the max-norm, clamped to [0, C-1]  (exact, done on the bit pattern)
+  const float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
+  int e = (int)((__float_as_uint(mx) >> 23) & 0xffu) - 126;
+  const int level = max(0, min((int)P.C - 1, e));
+  const float mip_bound = fminf(__uint_as_float((uint32_t)(127 + level) << 23), P.bound);
+  const float mip_rbound = 1 / mip_bound;
+  const uint32_t H = P.H;
+  // reference: (int)clamp(0.5 /*double*/ * (x*rb+1) * H, 0, H-1).  0.5*H is exact in float and the double product is
+  // exact, so one float multiply by (0.5f*H) rounds identically (DESIGN.md numerics contract).
+  const float halfH = 0.5f * (float)H, hm1 = (float)(H - 1);
+  const int nx = (int)clampf((x * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
+  const int ny = (int)clampf((y * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
+  const int nz = (int)clampf((z * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
+  const uint32_t cell = level * H * H * H + nx * H * H + ny * H + nz;
+  const bool occ = (__ldg(P.occupancy + (cell >> 5)) >> (cell & 31u)) & 1u;
+  if (occ) {
+    s.x = x; s.y = y; s.z = z;
+    const float dt = clampf(t * P.dt_gamma, P.dt_min, P.dt_max);
+    t += dt;
+    s.dt = dt;
+    s.cell = cell;
+    s.level = level;
+    return true;
+  }
+  const float tx = (((nx + 0.5f + 0.5f * copysignf(1.0f, d[0])) / hm1 * 2.0f - 1.0f) * mip_bound - x) * rd[0];
+  const float ty = (((ny + 0.5f + 0.5f * copysignf(1.0f, d[1])) / hm1 * 2.0f - 1.0f) * mip_bound - y) * rd[1];
+  const float tz = (((nz + 0.5f + 0.5f * copysignf(1.0f, d[2])) / hm1 * 2.0f - 1.0f) * mip_bound - z) * rd[2];
+  const float tt = t + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
+  do {
+    const float dt = clampf(t * P.dt_gamma, P.dt_min, P.dt_max);
+    t += dt;
+  } while (t < tt);
+  return false;
+}
+
+// block-wide sum / exclusive scan helpers (128 threads, warp shuffles)
+__device__ __forceinline__ int warp_incl_scan(int v) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int n = __shfl_up_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) >= o) v += n;
+  }
+  return v;
+}
+
+// Pass 1: rays for this shard + sample counts + per-block totals.
+// rays: float4 {dx,dy,dz,near}; fars; counts; block_sums[gridDim.x]
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
+k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, float4* __restrict__ rays,
+             float* __restrict__ fars, int* __restrict__ counts, int* __restrict__ block_sums) {
+  const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
+  int c = 0;
+  if (q < n_local) {
+    const int p = shard_pixel(map, q);
+    float d[3], near, far;
+    ray_dir(P, p, d);
+    near_far(P, d, near, far);
+    rays[q] = make_float4(d[0], d[1], d[2], near);
+    fars[q] = far;
+    const float rd[3] = {1 / d[0], 1 / d[1], 1 / d[2]};
+    float t = near;
+    Step s;
+    while (t < far && c < NRF_MAX_STEPS_D)
+      if (march_step(P, d, rd, t, s)) ++c;
+    counts[q] = c;
+  }
+  __shared__ int wsum[RAYS_BLOCK / 32];
+  const int incl = warp_incl_scan(c);
+  if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = incl;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int s = 0;
+#pragma unroll
+    for (int w = 0; w < RAYS_BLOCK / 32; ++w) s += wsum[w];
+    block_sums[blockIdx.x] = s;
+  }
+}
+
+// Count-only variant for externally supplied rays (stage probe nrf_probe_march).
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
+k_count_given(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays,
+              const float* __restrict__ fars, int* __restrict__ counts, int* __restrict__ block_sums) {
+  const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
+  int c = 0;
+  if (q < n) {
+    const float4 r = rays[q];
+    const float d[3] = {r.x, r.y, r.z};
+    const float rd[3] = {1 / d[0], 1 / d[1], 1 / d[2]};
+    const float far = fars[q];
+    float t = r.w;
+    Step s;
+    while (t < far && c < NRF_MAX_STEPS_D)
+      if (march_step(P, d, rd, t, s)) ++c;
+    counts[q] = c;
+  }
+  __shared__ int wsum[RAYS_BLOCK / 32];
+  const int incl = warp_incl_scan(c);
+  if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = incl;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int s = 0;
+#pragma unroll
+    for (int w = 0; w < RAYS_BLOCK / 32; ++w) s += wsum[w];
+    block_sums[blockIdx.x] = s;
+  }
+}
+
+// One-block exclusive scan of the per-block totals (in place); total[0] = sum, total[1] = #rays with samples is
+// accumulated elsewhere.  n_blocks <= 1024*64.
+extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict__ block_sums, int n_blocks,
+                                                                 unsigned long long* __restrict__ total) {
+  __shared__ int wsum[32];
+  __shared__ int carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (int base = 0; base < n_blocks; base += 1024) {
+    const int i = base + threadIdx.x;
+    const int v = (i < n_blocks) ? block_sums[i] : 0;
+    const int incl = warp_incl_scan(v);
+    if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      int w = wsum[threadIdx.x];
+      int wi = warp_incl_scan(w);
+      wsum[threadIdx.x] = wi - w;  // exclusive warp bases
+    }
+    __syncthreads();
+    const int carry = carry_s;
+    const int excl = carry + wsum[threadIdx.x >> 5] + incl - v;
+    if (i < n_blocks) block_sums[i] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_s = excl + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) total[0] = (unsigned long long)carry_s;
+}
+
+// Pass 2: re-march and emit the compact sample list.  ray_offsets[q] = first sample of ray q (exclusive scan).
+// samples: float4 {u,v,w,dt} (position already normalised: x*pos_w+0.5, nerf_render.cu:311-312), t_after, ray id.
+// dbg (optional, probe only): per sample {x,y,z,dt,t_after,level,cell,ray} raw.
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
+k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays, const float* __restrict__ fars,
+       const int* __restrict__ counts, const int* __restrict__ block_bases, int* __restrict__ ray_offsets,
+       float4* __restrict__ samples, float* __restrict__ t_after, int* __restrict__ sample_ray,
+       float* __restrict__ dbg, long long capacity) {
+  const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
+  const int c_total = (q < n) ? counts[q] : 0;
+  __shared__ int wsum[RAYS_BLOCK / 32];
+  const int incl = warp_incl_scan(c_total);
+  if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = incl;
+  __syncthreads();
+  int base = block_bases[blockIdx.x];
+  for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) base += wsum[w];
+  const long long first = (long long)base + incl - c_total;
+  if (q >= n) return;
+  ray_offsets[q] = (int)first;
+  if (c_total == 0 || first + c_total > capacity) return;
+  const float4 r = rays[q];
+  const float d[3] = {r.x, r.y, r.z};
+  const float rd[3] = {1 / d[0], 1 / d[1], 1 / d[2]};
+  const float far = fars[q];
+  float t = r.w;
+  int c = 0;
+  Step s;
+  while (t < far && c < c_total) {
+    if (!march_step(P, d, rd, t, s)) continue;
+    const long long k = first + c;
+    samples[k] = make_float4(P.pos_w * s.x + 0.5f, P.pos_w * s.y + 0.5f, P.pos_w * s.z + 0.5f, s.dt);
+    t_after[k] = t;
+    sample_ray[k] = q;
+    if (dbg) {
+      float* o = dbg + k * 8;
+      o[0] = s.x; o[1] = s.y; o[2] = s.z; o[3] = s.dt; o[4] = t;
+      o[5] = __int_as_float(s.level);
+      o[6] = __uint_as_float(s.cell);
+      o[7] = __int_as_float(q);
+    }
+    ++c;
+  }
+}
+
+// Load-time: float density grid -> occupancy bitfield, bit == (density > thresh)   (render_utils.h:560,619)
+extern "C" __global__ void k_build_occupancy(const float* __restrict__ grid, uint32_t n_cells, float thresh,
+                                             uint32_t* __restrict__ bits) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool occ = (i < n_cells) && (grid[i] > thresh);
+  const uint32_t m = __ballot_sync(0xffffffffu, occ);
+  if ((threadIdx.x & 31) == 0 && i < n_cells) bits[i >> 5] = m;
+}
+
+// Load-time: float32 params -> fp16 (nerf_network.h:434-436)
+extern "C" __global__ void k_cast_half(const float* __restrict__ in, __half* __restrict__ out, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = __float2half_rn(in[i]);
+}

@@ -1,0 +1,851 @@
+// nrf_api.cu — the C ABI (include/nerf_b200.h, include/nerf_b200_ext.h): context, model upload, per-frame
+// orchestration and the stage probes.  Host-side counterpart of ngp::NerfRender
+// (/root/reference/include/nerf-cuda/nerf_render.h:29-133, /root/reference/src/nerf_render.cu).
+//
+// Differences from the reference's host loop (src/nerf_render.cu:238-367), all deliberate:
+//   * 5 kernel launches and ONE 8-byte D2H read per frame instead of ~13 launches + a blocking D2H per wavefront
+//     iteration (up to 1024 iterations);
+//   * the network runs on exactly the live samples, not on the padded N_pad buffer every iteration;
+//   * n_gpus is a runtime value; each device renders interleaved pixel blocks and copies its u8 pixels straight
+//     into the pinned host frame (strided 2-D copy) — no CPU de-interleave loop;
+//   * there is no CPU path: without a CUDA device every compute entry point returns NRF_ENODEV.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "../../include/nerf_b200.h"
+#include "../../include/nerf_b200_ext.h"
+#include "nrf_device.cuh"
+#include "nrf_snapshot.h"
+
+// kernels (kernels_exact.cu, kernels_network.cu, kernels_composite.cu)
+extern "C" {
+__global__ void k_rays_count(const MarchParams P, ShardMap map, int n_local, float4* rays, float* fars, int* counts,
+                             int* block_sums);
+__global__ void k_count_given(const MarchParams P, int n, const float4* rays, const float* fars, int* counts,
+                              int* block_sums);
+__global__ void k_scan_blocks(int* block_sums, int n_blocks, unsigned long long* total);
+__global__ void k_emit(const MarchParams P, int n, const float4* rays, const float* fars, const int* counts,
+                       const int* block_bases, int* ray_offsets, float4* samples, float* t_after, int* sample_ray,
+                       float* dbg, long long capacity);
+__global__ void k_build_occupancy(const float* grid, uint32_t n_cells, float thresh, uint32_t* bits);
+__global__ void k_cast_half(const float* in, __half* out, size_t n);
+__global__ void k_composite(int n_rays, const int* ray_offsets, const int* counts, const float4* rays,
+                            const float* fars, const float4* samples, const float* t_after, const uint2* sample_out,
+                            float* rgb_f32, float* depth_f32, int* used_counts, uint8_t* rgb_u8, uint8_t* depth_u8);
+size_t nrf_network_smem_bytes();
+cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t stream, const NetParams* P, int n,
+                               const float4* samples, const int* sample_ray, const float4* rays, int dirs_mode,
+                               uint4* enc_io, uint2* out, uint32_t* idx_out);
+cudaError_t nrf_launch_network_simt(cudaStream_t stream, const NetParams* P, int n, const uint4* enc,
+                                    const float4* dirs01, uint2* out);
+int nrf_network_occupancy(int mode);
+}
+
+// ---------------------------------------------------------------------------------------------------- errors
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define CU(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e__ = (call);                                                                      \
+    if (e__ != cudaSuccess)                                                                        \
+      return fail(NRF_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+extern "C" const char* nrf_last_error(void) { return g_err; }
+extern "C" const char* nrf_version(void) { return "nerf_b200 0.1 (sm_100a)"; }
+
+// ---------------------------------------------------------------------------------------------------- level table
+// nerf_render.cu:147-165 (defaults) + tcnn grid.h:899-931 (offset table) + grid.h:186-187 (scale / resolution).
+// Computed on the HOST once; the kernels read scale/res from the table instead of re-deriving them with the
+// device's exp2f (DESIGN.md numerics contract).
+struct HostLevels {
+  uint32_t offsets[NRF_MAX_LEVELS + 1];
+  float scales[NRF_MAX_LEVELS];
+  uint32_t res[NRF_MAX_LEVELS];
+  float per_level_scale;
+};
+
+static int build_levels(const nrf_model_desc& d, HostLevels& lv) {
+  if (d.n_levels == 0 || d.n_levels > NRF_MAX_LEVELS) return fail(NRF_EINVAL, "n_levels=%u out of range", d.n_levels);
+  if (d.log2_hashmap_size == 0 || d.log2_hashmap_size > 28) return fail(NRF_EINVAL, "log2_hashmap_size out of range");
+  uint32_t base = d.base_resolution ? d.base_resolution : 1u << (d.log2_hashmap_size / 3);
+  float pls = d.per_level_scale;
+  if (pls <= 0.0f && d.n_levels > 1) pls = std::exp(std::log(2048.0f * (float)d.bound / (float)base) / (d.n_levels - 1));
+  lv.per_level_scale = pls;
+  const float log2_pls = std::log2(pls);
+  uint32_t offset = 0;
+  for (uint32_t i = 0; i < d.n_levels; ++i) {
+    const float scale = exp2f(i * log2_pls) * base - 1.0f;
+    const uint32_t resolution = (uint32_t)(ceilf(scale)) + 1;
+    const uint32_t max_params = std::numeric_limits<uint32_t>::max() / 2;
+    uint32_t n = std::pow((float)resolution, 3) > (float)max_params ? max_params : resolution * resolution * resolution;
+    n = (n + 7u) / 8u * 8u;
+    n = std::min(n, 1u << d.log2_hashmap_size);
+    lv.offsets[i] = offset;
+    lv.scales[i] = scale;
+    lv.res[i] = resolution;
+    offset += n;
+  }
+  lv.offsets[d.n_levels] = offset;
+  return NRF_OK;
+}
+
+static int check_arch(const nrf_model_desc& d) {
+  if (d.n_levels != 16 || d.n_features_per_level != 2 || d.n_neurons != 64 || d.density_hidden_layers != 1 ||
+      d.rgb_hidden_layers != 2 || d.sh_degree != 4)
+    return fail(NRF_EINVAL,
+                "unsupported architecture (need L=16 F=2 width=64 density_hidden=1 rgb_hidden=2 sh_degree=4, got L=%u "
+                "F=%u width=%u dh=%u rh=%u sh=%u)",
+                d.n_levels, d.n_features_per_level, d.n_neurons, d.density_hidden_layers, d.rgb_hidden_layers,
+                d.sh_degree);
+  if (d.rgb_activation > NRF_ACT_SIGMOID || d.sigma_activation > NRF_ACT_SIGMOID)
+    return fail(NRF_EINVAL, "unsupported activation id");
+  if (!(d.bound > 0) || d.cascades == 0 || d.cascades > 8 || d.grid_size == 0 || d.grid_size > 512 ||
+      (d.grid_size * d.grid_size * d.grid_size) % 32 != 0)
+    return fail(NRF_EINVAL, "bad scene description (bound/cascades/grid_size)");
+  return NRF_OK;
+}
+
+extern "C" int nrf_level_table(const nrf_model_desc* desc, uint32_t* offsets, float* scales, uint32_t* resolutions) {
+  if (!desc) return fail(NRF_EINVAL, "null desc");
+  HostLevels lv;
+  int rc = build_levels(*desc, lv);
+  if (rc) return rc;
+  for (uint32_t i = 0; i <= desc->n_levels; ++i)
+    if (offsets) offsets[i] = lv.offsets[i];
+  for (uint32_t i = 0; i < desc->n_levels; ++i) {
+    if (scales) scales[i] = lv.scales[i];
+    if (resolutions) resolutions[i] = lv.res[i];
+  }
+  return NRF_OK;
+}
+
+extern "C" int nrf_param_count(const nrf_model_desc* desc, uint64_t* n_params) {
+  if (!desc || !n_params) return fail(NRF_EINVAL, "null argument");
+  HostLevels lv;
+  int rc = build_levels(*desc, lv);
+  if (rc) return rc;
+  *n_params = 10240ull + 2ull * lv.offsets[desc->n_levels];
+  return NRF_OK;
+}
+
+// fp32 -> fp16 bits on the host (RN), used only to pre-pack the 20 KB of MLP weights
+static uint16_t f2h_bits(float f) {
+  __half h = __float2half_rn(f);
+  uint16_t b;
+  std::memcpy(&b, &h, 2);
+  return b;
+}
+
+// Pack W[n_out][n_in] (row-major, reference order fully_fused_mlp.cu:662-686) into the tcgen05 K-major SWIZZLE_NONE
+// core-matrix order used by kernels_network.cu: byte offset (k/8)*(N*16) + n*16 + (k%8)*2.
+static void pack_weight(const float* W, int n_out, int n_in, uint16_t* dst) {
+  for (int n = 0; n < n_out; ++n)
+    for (int k = 0; k < n_in; ++k) dst[(k / 8) * (n_out * 8) + n * 8 + (k % 8)] = f2h_bits(W[n * n_in + k]);
+}
+
+// ---------------------------------------------------------------------------------------------------- context
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  cudaError_t ensure(size_t want) {
+    if (want <= n) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+    cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+    if (e == cudaSuccess) n = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+
+struct Device {
+  int dev = 0, n_sms = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[6] = {};
+  ShardMap map{0, 1, 1, 0};
+  int n_local = 0;
+  // model replica
+  DevBuf<__half> params_h;     // all params as fp16 (mlp row-major 10240 | table)
+  DevBuf<uint4> mlp_packed;    // 1280 x 16 B
+  DevBuf<uint32_t> occupancy;
+  NetParams net{};
+  MarchParams march{};
+  // per-frame buffers
+  DevBuf<float4> rays, samples;
+  DevBuf<float> fars, t_after, rgb_f32, depth_f32;
+  DevBuf<int> counts, ray_offsets, block_sums, sample_ray, used;
+  DevBuf<uint2> sample_out;
+  DevBuf<uint8_t> rgb_u8, depth_u8;
+  DevBuf<unsigned long long> total;
+  unsigned long long* total_h = nullptr;  // pinned
+  // probe scratch
+  DevBuf<uint4> enc;
+  DevBuf<uint32_t> idx;
+  DevBuf<float> dbg;
+  unsigned long long last_samples = 0;
+};
+
+struct nrf_ctx {
+  std::vector<Device> devs;
+  nrf_model_desc desc{};
+  HostLevels levels{};
+  float aabb[6] = {};
+  bool loaded = false;
+  int W = 0, H = 0;
+  int shard = 0, n_shards = 1, block_pixels = 1024;  // process-level sharding (torchrun); devices subdivide further
+  uint8_t* rgb_host = nullptr;    // pinned, W*H*3 (full frame when n_shards == 1, else local rays packed)
+  uint8_t* depth_host = nullptr;  // pinned, W*H
+  nrf_stats stats{};
+  int net_grid_ctas_per_sm = 0;
+};
+
+static int device_count() {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
+  if (!out || n_gpus < 1) return fail(NRF_EINVAL, "nrf_create: bad arguments");
+  const int avail = device_count();
+  if (avail < 1) return fail(NRF_ENODEV, "no CUDA device available (this library has no CPU path)");
+  if (n_gpus > avail && !device_ids) return fail(NRF_ENODEV, "requested %d GPUs, %d available", n_gpus, avail);
+  nrf_ctx* c = new nrf_ctx();
+  c->devs.resize(n_gpus);
+  for (int g = 0; g < n_gpus; ++g) {
+    Device& D = c->devs[g];
+    D.dev = device_ids ? device_ids[g] : g;
+    cudaError_t e = cudaSetDevice(D.dev);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&D.stream, cudaStreamNonBlocking);
+    for (int k = 0; k < 6 && e == cudaSuccess; ++k) e = cudaEventCreate(&D.ev[k]);
+    if (e == cudaSuccess) e = cudaMallocHost(&D.total_h, 4 * sizeof(unsigned long long));
+    cudaDeviceProp prop;
+    if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, D.dev);
+    if (e != cudaSuccess) {
+      delete c;
+      return fail(NRF_ECUDA, "device %d init failed: %s", D.dev, cudaGetErrorString(e));
+    }
+    if (prop.major != 10) {
+      delete c;
+      return fail(NRF_ENODEV, "device %d is sm_%d%d; this library contains sm_100a code only", D.dev, prop.major, prop.minor);
+    }
+    D.n_sms = prop.multiProcessorCount;
+  }
+  *out = c;
+  return NRF_OK;
+}
+
+static void free_device(Device& D) {
+  cudaSetDevice(D.dev);
+  D.params_h.release(); D.mlp_packed.release(); D.occupancy.release();
+  D.rays.release(); D.samples.release(); D.fars.release(); D.t_after.release(); D.rgb_f32.release();
+  D.depth_f32.release(); D.counts.release(); D.ray_offsets.release(); D.block_sums.release();
+  D.sample_ray.release(); D.used.release(); D.sample_out.release(); D.rgb_u8.release(); D.depth_u8.release();
+  D.total.release(); D.enc.release(); D.idx.release(); D.dbg.release();
+  if (D.total_h) cudaFreeHost(D.total_h);
+  for (int k = 0; k < 6; ++k) if (D.ev[k]) cudaEventDestroy(D.ev[k]);
+  if (D.stream) cudaStreamDestroy(D.stream);
+}
+
+extern "C" int nrf_destroy(nrf_ctx* c) {
+  if (!c) return NRF_OK;
+  for (Device& D : c->devs) free_device(D);
+  if (c->rgb_host) cudaFreeHost(c->rgb_host);
+  if (c->depth_host) cudaFreeHost(c->depth_host);
+  delete c;
+  return NRF_OK;
+}
+
+// Upload a model replica to one device: params fp32 -> fp16 (nerf_network.h:434-436), MLP pre-packed for UMMA,
+// density grid -> occupancy bitfield with thresh = min(0.01, mean_density) (render_utils.h:560,619).
+static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_params, const float* grid, size_t n_grid) {
+  CU(cudaSetDevice(D.dev));
+  const nrf_model_desc& d = c->desc;
+  DevBuf<float> tmp;
+  const size_t chunk = std::max(n_params, n_grid);
+  CU(tmp.ensure(chunk));
+  CU(D.params_h.ensure(n_params));
+  CU(cudaMemcpyAsync(tmp.p, params, n_params * sizeof(float), cudaMemcpyHostToDevice, D.stream));
+  k_cast_half<<<(unsigned)((n_params + 255) / 256), 256, 0, D.stream>>>(tmp.p, D.params_h.p, n_params);
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(D.stream));
+  // occupancy
+  CU(D.occupancy.ensure(n_grid / 32));
+  CU(cudaMemcpyAsync(tmp.p, grid, n_grid * sizeof(float), cudaMemcpyHostToDevice, D.stream));
+  k_build_occupancy<<<(unsigned)((n_grid + 255) / 256), 256, 0, D.stream>>>(tmp.p, (uint32_t)n_grid,
+                                                                          fminf(0.01f, d.mean_density), D.occupancy.p);
+  CU(cudaGetLastError());
+  // packed MLP weights
+  std::vector<uint16_t> packed(10240);
+  pack_weight(params + 0, 64, 32, packed.data() + 0);
+  pack_weight(params + 2048, 16, 64, packed.data() + 2048);
+  pack_weight(params + 3072, 64, 32, packed.data() + 3072);
+  pack_weight(params + 5120, 64, 64, packed.data() + 5120);
+  pack_weight(params + 9216, 16, 64, packed.data() + 9216);
+  CU(D.mlp_packed.ensure(1280));
+  CU(cudaMemcpyAsync(D.mlp_packed.p, packed.data(), 20480, cudaMemcpyHostToDevice, D.stream));
+  CU(cudaStreamSynchronize(D.stream));
+  tmp.release();
+  // parameter blocks
+  NetParams& N = D.net;
+  for (uint32_t l = 0; l < d.n_levels; ++l) {
+    LevelInfo& L = N.lv[l];
+    L.offset = c->levels.offsets[l];
+    L.size = c->levels.offsets[l + 1] - c->levels.offsets[l];
+    L.res = c->levels.res[l];
+    L.scale = c->levels.scales[l];
+    // grid_index (grid.h:100-117): hash iff T_l < res^3 (the stride loop stops early instead of overflowing)
+    const double dense = (double)L.res * L.res * L.res;
+    L.hashed = dense > (double)L.size ? 1u : 0u;
+    if (L.hashed && (L.size & (L.size - 1)) != 0) return fail(NRF_EINVAL, "hashed level %u size %u not a power of two", l, L.size);
+  }
+  N.mlp_rowmaj = D.params_h.p;
+  N.table = reinterpret_cast<const __half2*>(D.params_h.p + 10240);
+  N.mlp_packed = D.mlp_packed.p;
+  N.rgb_act = d.rgb_activation;
+  N.sigma_act = d.sigma_activation;
+  MarchParams& M = D.march;
+  std::memcpy(M.aabb, c->aabb, 24);
+  M.bound = d.bound;
+  M.dt_gamma = 1.0 / 128;                         // nerf_render.h:66
+  M.dt_min = 2 * 1.7320508075688772f / 1024;      // render_utils.h:179-183
+  M.dt_max = 2 * d.bound / d.grid_size;           // render_utils.h:581
+  M.min_near = 0.2f;                              // nerf_render.h:76
+  M.pos_w = 1.0 / (2 * d.bound);                  // nerf_render.cu:311-312
+  M.C = d.cascades;
+  M.H = d.grid_size;
+  M.occupancy = D.occupancy.p;
+  return NRF_OK;
+}
+
+extern "C" int nrf_load_raw(nrf_ctx* c, const nrf_model_desc* desc, const float* params, size_t n_params,
+                            const float* density_grid, size_t n_grid, const float aabb[6]) {
+  if (!c || !desc || !params || !density_grid || !aabb) return fail(NRF_EINVAL, "nrf_load_raw: null argument");
+  int rc = check_arch(*desc);
+  if (rc) return rc;
+  HostLevels lv;
+  rc = build_levels(*desc, lv);
+  if (rc) return rc;
+  const size_t want = 10240 + 2 * (size_t)lv.offsets[desc->n_levels];
+  if (n_params != want)  // nerf_network.h:425-427 param-count check
+    return fail(NRF_EFORMAT, "Can't set params because CPU buffer has the wrong size: got %zu, expected %zu", n_params, want);
+  const size_t cells = (size_t)desc->grid_size * desc->grid_size * desc->grid_size * desc->cascades;
+  if (n_grid != cells) return fail(NRF_EFORMAT, "Incompatible number of grid cascades.");  // nerf_render.cu:467-469
+  c->desc = *desc;
+  c->desc.per_level_scale = lv.per_level_scale;
+  if (!c->desc.base_resolution) c->desc.base_resolution = 1u << (desc->log2_hashmap_size / 3);
+  c->levels = lv;
+  std::memcpy(c->aabb, aabb, 24);
+  for (Device& D : c->devs) {
+    rc = upload_model(c, D, params, n_params, density_grid, n_grid);
+    if (rc) return rc;
+  }
+  c->loaded = true;
+  return NRF_OK;
+}
+
+extern "C" int nrf_load_snapshot(nrf_ctx* c, const char* path) {
+  if (!c || !path) return fail(NRF_EINVAL, "nrf_load_snapshot: null argument");
+  const std::string p(path);
+  // reload_network_from_file accepts only .msgpack (nerf_render.cu:98,105-107)
+  if (p.size() < 8 || p.substr(p.size() - 8) != ".msgpack")
+    return fail(NRF_EIO, "Network config %s must be a .msgpack snapshot.", path);
+  FILE* f = std::fopen(path, "rb");
+  if (!f) return fail(NRF_EIO, "Network config %s does not exist.", path);  // nerf_render.cu:73-76
+  std::fseek(f, 0, SEEK_END);
+  const long sz = std::ftell(f);
+  std::fseek(f, 0, SEEK_SET);
+  std::vector<uint8_t> buf((size_t)std::max(0L, sz));
+  const size_t got = sz > 0 ? std::fread(buf.data(), 1, (size_t)sz, f) : 0;
+  std::fclose(f);
+  if ((long)got != sz) return fail(NRF_EIO, "short read on %s", path);
+  nrf::Snapshot snap;
+  try {
+    nrf::parse_snapshot(buf.data(), buf.size(), p, snap);
+  } catch (const std::exception& e) {
+    return fail(NRF_EFORMAT, "%s", e.what());
+  }
+  return nrf_load_raw(c, &snap.desc, snap.params.data(), snap.params.size(), snap.density_grid.data(),
+                      snap.density_grid.size(), snap.aabb);
+}
+
+extern "C" int nrf_get_model_desc(nrf_ctx* c, nrf_model_desc* out) {
+  if (!c || !out) return fail(NRF_EINVAL, "null argument");
+  if (!c->loaded) return fail(NRF_ESTATE, "no model loaded");
+  *out = c->desc;
+  return NRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- resolution
+extern "C" int nrf_set_shard(nrf_ctx* c, int shard, int n_shards, int block_pixels) {
+  if (!c || n_shards < 1 || shard < 0 || shard >= n_shards || block_pixels < 1)
+    return fail(NRF_EINVAL, "nrf_set_shard: bad arguments");
+  c->shard = shard;
+  c->n_shards = n_shards;
+  c->block_pixels = block_pixels;
+  c->W = c->H = 0;  // force re-allocation on the next set_resolution
+  return NRF_OK;
+}
+
+// NerfRender::set_resolution (nerf_render.cu:186-236).  Idempotent (reference defect D7).
+extern "C" int nrf_set_resolution(nrf_ctx* c, int W, int H) {
+  if (!c || W < 1 || H < 1) return fail(NRF_EINVAL, "nrf_set_resolution: bad arguments");
+  if (!c->loaded) return fail(NRF_ESTATE, "set_resolution must follow reload_network_from_file");  // nerf_render.cu:226
+  if ((long long)W * H > (1ll << 30)) return fail(NRF_EINVAL, "resolution too large");
+  if (c->W == W && c->H == H) return NRF_OK;
+  const int n_dev = (int)c->devs.size();
+  const int total_shards = c->n_shards * n_dev;
+  for (int g = 0; g < n_dev; ++g) {
+    Device& D = c->devs[g];
+    CU(cudaSetDevice(D.dev));
+    D.map = ShardMap{c->shard * n_dev + g, total_shards, total_shards == 1 ? 1 : c->block_pixels, W * H};
+    D.n_local = shard_local_count(D.map);
+    const size_t N = (size_t)std::max(D.n_local, 1);
+    const size_t nb = (N + 127) / 128;
+    CU(D.rays.ensure(N)); CU(D.fars.ensure(N)); CU(D.counts.ensure(N)); CU(D.ray_offsets.ensure(N));
+    CU(D.block_sums.ensure(nb)); CU(D.used.ensure(N)); CU(D.rgb_f32.ensure(N * 3)); CU(D.depth_f32.ensure(N));
+    CU(D.rgb_u8.ensure(N * 3)); CU(D.depth_u8.ensure(N)); CU(D.total.ensure(4));
+    D.march.W = W;
+  }
+  if (c->rgb_host) cudaFreeHost(c->rgb_host);
+  if (c->depth_host) cudaFreeHost(c->depth_host);
+  c->rgb_host = c->depth_host = nullptr;
+  CU(cudaMallocHost(&c->rgb_host, (size_t)W * H * 3));
+  CU(cudaMallocHost(&c->depth_host, (size_t)W * H));
+  c->W = W;
+  c->H = H;
+  return NRF_OK;
+}
+
+extern "C" int nrf_local_rays(nrf_ctx* c, int* n_local) {
+  if (!c || !n_local) return fail(NRF_EINVAL, "null argument");
+  if (!c->W) return fail(NRF_ESTATE, "set_resolution not called");
+  int n = 0;
+  for (Device& D : c->devs) n += D.n_local;
+  *n_local = n;
+  return NRF_OK;
+}
+
+extern "C" int nrf_shard_pixel(nrf_ctx* c, int q, int* pixel) {
+  if (!c || !pixel || !c->W) return fail(NRF_EINVAL, "bad argument / state");
+  *pixel = shard_pixel(c->devs[0].map, q);
+  return NRF_OK;
+}
+
+extern "C" int nrf_device_outputs(nrf_ctx* c, void** rgb_u8, void** depth_u8, void** rgb_f32) {
+  if (!c || !c->W) return fail(NRF_ESTATE, "set_resolution not called");
+  if (rgb_u8) *rgb_u8 = c->devs[0].rgb_u8.p;
+  if (depth_u8) *depth_u8 = c->devs[0].depth_u8.p;
+  if (rgb_f32) *rgb_f32 = c->devs[0].rgb_f32.p;
+  return NRF_OK;
+}
+
+extern "C" int nrf_stream(nrf_ctx* c, void** stream) {
+  if (!c || !stream) return fail(NRF_EINVAL, "null argument");
+  *stream = (void*)c->devs[0].stream;
+  return NRF_OK;
+}
+
+extern "C" int nrf_synchronize(nrf_ctx* c) {
+  if (!c) return fail(NRF_EINVAL, "null ctx");
+  for (Device& D : c->devs) {
+    CU(cudaSetDevice(D.dev));
+    CU(cudaStreamSynchronize(D.stream));
+  }
+  return NRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- frame
+// nerf_matrix_to_ngp (render_utils.h:68-77): rows (1,2,0), columns 1,2 negated, translation * scale (+ offset 0).
+static void set_pose(nrf_ctx* c, MarchParams& M, const float intr[4], const float* P) {
+  const int rows[3] = {1, 2, 0};
+  for (int r = 0; r < 3; ++r) {
+    const float* src = P + rows[r] * 4;
+    M.R[r * 3 + 0] = src[0];
+    M.R[r * 3 + 1] = -src[1];
+    M.R[r * 3 + 2] = -src[2];
+    M.o[r] = src[3] * c->desc.scale + 0.0f;
+  }
+  std::memcpy(M.intr, intr, 16);
+}
+
+static int network_grid(nrf_ctx* c, const Device& D, int n_samples) {
+  if (!c->net_grid_ctas_per_sm) c->net_grid_ctas_per_sm = std::max(1, nrf_network_occupancy(2));
+  const int tiles = (n_samples + NRF_TILE - 1) / NRF_TILE;
+  return std::max(1, std::min(tiles, D.n_sms * c->net_grid_ctas_per_sm));
+}
+
+// Phase A (async): rays + count + scan, then the 8-byte total read-back.
+static int frame_phase_a(nrf_ctx* c, Device& D, const float intr[4], const float* pose) {
+  CU(cudaSetDevice(D.dev));
+  set_pose(c, D.march, intr, pose);
+  const int nb = (D.n_local + 127) / 128;
+  CU(cudaEventRecord(D.ev[0], D.stream));
+  if (D.n_local > 0) {
+    k_rays_count<<<nb, 128, 0, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.fars.p, D.counts.p, D.block_sums.p);
+    CU(cudaGetLastError());
+  }
+  k_scan_blocks<<<1, 1024, 0, D.stream>>>(D.block_sums.p, D.n_local > 0 ? nb : 0, D.total.p);
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(D.ev[1], D.stream));
+  CU(cudaMemcpyAsync(D.total_h, D.total.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, D.stream));
+  return NRF_OK;
+}
+
+// Phase B: emit + network + composite (+ optional D2H of the u8 frame).
+static int frame_phase_b(nrf_ctx* c, Device& D, bool to_host) {
+  CU(cudaSetDevice(D.dev));
+  CU(cudaStreamSynchronize(D.stream));
+  const unsigned long long S = D.total_h[0];
+  if (S > (1ull << 31) - 256) return fail(NRF_EINVAL, "frame produces %llu samples (> 2^31)", S);
+  D.last_samples = S;
+  const size_t cap = std::max<size_t>((size_t)S, 1);
+  if (cap > D.samples.n) {
+    const size_t want = cap + cap / 4;
+    CU(D.samples.ensure(want)); CU(D.t_after.ensure(want)); CU(D.sample_ray.ensure(want)); CU(D.sample_out.ensure(want));
+  }
+  const int nb = (D.n_local + 127) / 128;
+  if (D.n_local > 0) {
+    k_emit<<<nb, 128, 0, D.stream>>>(D.march, D.n_local, D.rays.p, D.fars.p, D.counts.p, D.block_sums.p,
+                                    D.ray_offsets.p, D.samples.p, D.t_after.p, D.sample_ray.p, nullptr,
+                                    (long long)D.samples.n);
+    CU(cudaGetLastError());
+  }
+  CU(cudaEventRecord(D.ev[2], D.stream));
+  CU(nrf_launch_network(2, network_grid(c, D, (int)S), D.stream, &D.net, (int)S, D.samples.p, D.sample_ray.p, D.rays.p,
+                        0, nullptr, D.sample_out.p, nullptr));
+  CU(cudaEventRecord(D.ev[3], D.stream));
+  if (D.n_local > 0) {
+    const int blocks = (int)(((size_t)D.n_local * 32 + 255) / 256);
+    k_composite<<<blocks, 256, 0, D.stream>>>(D.n_local, D.ray_offsets.p, D.counts.p, D.rays.p, D.fars.p, D.samples.p,
+                                              D.t_after.p, D.sample_out.p, D.rgb_f32.p, D.depth_f32.p, D.used.p,
+                                              D.rgb_u8.p, D.depth_u8.p);
+    CU(cudaGetLastError());
+  }
+  CU(cudaEventRecord(D.ev[4], D.stream));
+  if (to_host && D.n_local > 0) {
+    // scatter this device's packed pixels into the full host frame: blocks of `block` pixels at stride n_shards*block
+    const ShardMap& m = D.map;
+    if (m.n_shards == 1 || c->n_shards > 1) {
+      // single shard, or process-level sharding (host buffer is packed in local order; the gather is NCCL's job)
+      size_t off = 0;
+      if (c->n_shards > 1) for (const Device& E : c->devs) { if (&E == &D) break; off += E.n_local; }
+      CU(cudaMemcpyAsync(c->rgb_host + off * 3, D.rgb_u8.p, (size_t)D.n_local * 3, cudaMemcpyDeviceToHost, D.stream));
+      CU(cudaMemcpyAsync(c->depth_host + off, D.depth_u8.p, (size_t)D.n_local, cudaMemcpyDeviceToHost, D.stream));
+    } else {
+      const int full = D.n_local / m.block, tail = D.n_local - full * m.block;
+      const size_t bs = (size_t)m.block;
+      if (full > 0) {
+        CU(cudaMemcpy2DAsync(c->rgb_host + (size_t)m.shard * bs * 3, (size_t)m.n_shards * bs * 3, D.rgb_u8.p, bs * 3,
+                             bs * 3, full, cudaMemcpyDeviceToHost, D.stream));
+        CU(cudaMemcpy2DAsync(c->depth_host + (size_t)m.shard * bs, (size_t)m.n_shards * bs, D.depth_u8.p, bs, bs, full,
+                             cudaMemcpyDeviceToHost, D.stream));
+      }
+      if (tail > 0) {
+        const size_t p0 = (size_t)shard_pixel(m, full * m.block);
+        CU(cudaMemcpyAsync(c->rgb_host + p0 * 3, D.rgb_u8.p + (size_t)full * bs * 3, (size_t)tail * 3,
+                           cudaMemcpyDeviceToHost, D.stream));
+        CU(cudaMemcpyAsync(c->depth_host + p0, D.depth_u8.p + (size_t)full * bs, (size_t)tail, cudaMemcpyDeviceToHost,
+                           D.stream));
+      }
+    }
+  }
+  CU(cudaEventRecord(D.ev[5], D.stream));
+  return NRF_OK;
+}
+
+static int render_common(nrf_ctx* c, const float intr[4], const float* pose, bool to_host, bool sync) {
+  if (!c || !intr || !pose) return fail(NRF_EINVAL, "render: null argument");
+  if (!c->loaded) return fail(NRF_ESTATE, "render_frame before reload_network_from_file");
+  if (!c->W) return fail(NRF_ESTATE, "render_frame before set_resolution");
+  for (Device& D : c->devs) { int rc = frame_phase_a(c, D, intr, pose); if (rc) return rc; }
+  for (Device& D : c->devs) { int rc = frame_phase_b(c, D, to_host); if (rc) return rc; }
+  if (sync) {
+    for (Device& D : c->devs) { CU(cudaSetDevice(D.dev)); CU(cudaStreamSynchronize(D.stream)); }
+  }
+  return NRF_OK;
+}
+
+extern "C" int nrf_render_frame(nrf_ctx* c, const float intr[4], const float pose[16], uint8_t** rgb, uint8_t** depth) {
+  int rc = render_common(c, intr, pose, true, true);
+  if (rc) return rc;
+  if (rgb) *rgb = c->rgb_host;
+  if (depth) *depth = c->depth_host;
+  return NRF_OK;
+}
+
+extern "C" int nrf_render_frame_device(nrf_ctx* c, const float intr[4], const float pose[16]) {
+  return render_common(c, intr, pose, false, false);
+}
+
+extern "C" int nrf_render_batch(nrf_ctx* c, const float intr[4], const float* poses, int n_poses, uint8_t* rgb_out) {
+  if (!rgb_out || n_poses < 0) return fail(NRF_EINVAL, "nrf_render_batch: bad arguments");
+  int n_local = 0;
+  int rc = nrf_local_rays(c, &n_local);
+  if (rc) return rc;
+  const size_t frame_bytes = (c->n_shards == 1 ? (size_t)c->W * c->H : (size_t)n_local) * 3;
+  for (int i = 0; i < n_poses; ++i) {
+    rc = render_common(c, intr, poses + (size_t)i * 16, true, true);
+    if (rc) return rc;
+    std::memcpy(rgb_out + (size_t)i * frame_bytes, c->rgb_host, frame_bytes);
+  }
+  return NRF_OK;
+}
+
+extern "C" int nrf_get_float_frame(nrf_ctx* c, float* rgb_f32, float* depth_f32, int32_t* samples_per_ray) {
+  if (!c || !c->W) return fail(NRF_ESTATE, "no frame rendered");
+  // gathers in GLOBAL pixel order when the context covers the whole frame, else in local order
+  const bool whole = c->n_shards == 1;
+  size_t off = 0;
+  for (Device& D : c->devs) {
+    CU(cudaSetDevice(D.dev));
+    CU(cudaStreamSynchronize(D.stream));
+    const int n = D.n_local;
+    std::vector<float> r((size_t)n * 3), d(n);
+    std::vector<int> u(n);
+    if (n) {
+      CU(cudaMemcpy(r.data(), D.rgb_f32.p, (size_t)n * 12, cudaMemcpyDeviceToHost));
+      CU(cudaMemcpy(d.data(), D.depth_f32.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+      CU(cudaMemcpy(u.data(), D.used.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    }
+    for (int q = 0; q < n; ++q) {
+      const size_t p = whole ? (size_t)shard_pixel(D.map, q) : off + q;
+      if (rgb_f32) std::memcpy(rgb_f32 + p * 3, &r[(size_t)q * 3], 12);
+      if (depth_f32) depth_f32[p] = d[q];
+      if (samples_per_ray) samples_per_ray[p] = u[q];
+    }
+    off += n;
+  }
+  return NRF_OK;
+}
+
+extern "C" int nrf_get_stats(nrf_ctx* c, nrf_stats* out) {
+  if (!c || !out) return fail(NRF_EINVAL, "null argument");
+  if (!c->W) return fail(NRF_ESTATE, "no frame rendered");
+  nrf_stats s{};
+  s.n_rays = (uint64_t)c->W * c->H;
+  s.n_gpus = (uint32_t)c->devs.size();
+  s.n_launches = 5 * s.n_gpus;
+  for (Device& D : c->devs) {
+    CU(cudaSetDevice(D.dev));
+    CU(cudaStreamSynchronize(D.stream));
+    s.n_samples += D.last_samples;
+  }
+  Device& D0 = c->devs[0];
+  CU(cudaSetDevice(D0.dev));
+  float ms;
+  CU(cudaEventElapsedTime(&ms, D0.ev[0], D0.ev[1])); s.ms_setup = ms;   // rays + count + scan (march pass 1)
+  CU(cudaEventElapsedTime(&ms, D0.ev[1], D0.ev[2])); s.ms_march = ms;   // read-back + emit (march pass 2)
+  CU(cudaEventElapsedTime(&ms, D0.ev[2], D0.ev[3])); s.ms_network = ms;
+  CU(cudaEventElapsedTime(&ms, D0.ev[3], D0.ev[4])); s.ms_composite = ms;
+  CU(cudaEventElapsedTime(&ms, D0.ev[0], D0.ev[5])); s.ms_total = ms;
+  *out = s;
+  return NRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- stage probes
+#define NEED_MODEL(c)                                                        \
+  do {                                                                       \
+    if (!(c)) return fail(NRF_EINVAL, "null ctx");                           \
+    if (!(c)->loaded) return fail(NRF_ESTATE, "no model loaded");            \
+  } while (0)
+
+extern "C" int nrf_probe_rays(nrf_ctx* c, const float intr[4], const float pose[16], int W, int H, int pix0, int n,
+                              float rays_o[3], float* rays_d, float* nears, float* fars) {
+  NEED_MODEL(c);
+  if (n < 0 || pix0 < 0 || (long long)pix0 + n > (long long)W * H) return fail(NRF_EINVAL, "pixel range out of frame");
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  MarchParams M = D.march;
+  set_pose(c, M, intr, pose);
+  M.W = W;
+  for (int k = 0; k < 3; ++k) rays_o[k] = M.o[k];
+  if (n == 0) return NRF_OK;
+  DevBuf<float4> r; DevBuf<float> f; DevBuf<int> cnt, bs;
+  const int nb = (n + 127) / 128;
+  CU(r.ensure(n)); CU(f.ensure(n)); CU(cnt.ensure(n)); CU(bs.ensure(nb));
+  // a shard map that starts at pix0: one shard, identity, offset applied by rendering [0, pix0+n) lazily is wasteful;
+  // instead use block == n, n_shards large enough that shard index selects the window when pix0 % n == 0, else fall
+  // back to rendering from 0.
+  ShardMap map{0, 1, 1, pix0 + n};
+  DevBuf<float4> rall; DevBuf<float> fall; DevBuf<int> call;
+  const int ntot = pix0 + n, nbt = (ntot + 127) / 128;
+  CU(rall.ensure(ntot)); CU(fall.ensure(ntot)); CU(call.ensure(ntot)); CU(bs.ensure(nbt));
+  k_rays_count<<<nbt, 128, 0, D.stream>>>(M, map, ntot, rall.p, fall.p, call.p, bs.p);
+  CU(cudaGetLastError());
+  std::vector<float4> hr(n);
+  CU(cudaMemcpyAsync(hr.data(), rall.p + pix0, (size_t)n * 16, cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaMemcpyAsync(fars, fall.p + pix0, (size_t)n * 4, cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaStreamSynchronize(D.stream));
+  for (int i = 0; i < n; ++i) {
+    rays_d[i * 3 + 0] = hr[i].x; rays_d[i * 3 + 1] = hr[i].y; rays_d[i * 3 + 2] = hr[i].z;
+    nears[i] = hr[i].w;
+  }
+  r.release(); f.release(); cnt.release(); bs.release(); rall.release(); fall.release(); call.release();
+  return NRF_OK;
+}
+
+extern "C" int nrf_probe_march(nrf_ctx* c, int n, const float rays_o[3], const float* rays_d, const float* nears,
+                               const float* fars, int32_t* counts, float* samples, size_t max_samples) {
+  NEED_MODEL(c);
+  if (n <= 0) return n == 0 ? NRF_OK : fail(NRF_EINVAL, "n < 0");
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  MarchParams M = D.march;
+  for (int k = 0; k < 3; ++k) M.o[k] = rays_o[k];
+  std::vector<float4> hr(n);
+  for (int i = 0; i < n; ++i) hr[i] = make_float4(rays_d[i * 3], rays_d[i * 3 + 1], rays_d[i * 3 + 2], nears[i]);
+  DevBuf<float4> r, smp; DevBuf<float> f, ta, dbg; DevBuf<int> cnt, bs, offs, sray; DevBuf<unsigned long long> tot;
+  const int nb = (n + 127) / 128;
+  CU(r.ensure(n)); CU(f.ensure(n)); CU(cnt.ensure(n)); CU(bs.ensure(nb)); CU(offs.ensure(n)); CU(tot.ensure(4));
+  CU(cudaMemcpyAsync(r.p, hr.data(), (size_t)n * 16, cudaMemcpyHostToDevice, D.stream));
+  CU(cudaMemcpyAsync(f.p, fars, (size_t)n * 4, cudaMemcpyHostToDevice, D.stream));
+  k_count_given<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p);
+  CU(cudaGetLastError());
+  k_scan_blocks<<<1, 1024, 0, D.stream>>>(bs.p, nb, tot.p);
+  CU(cudaGetLastError());
+  unsigned long long S = 0;
+  CU(cudaMemcpyAsync(&S, tot.p, 8, cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaMemcpyAsync(counts, cnt.p, (size_t)n * 4, cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaStreamSynchronize(D.stream));
+  int rc = NRF_OK;
+  if (samples) {
+    if (S > max_samples) rc = fail(NRF_EINVAL, "sample buffer too small: need %llu", S);
+    else if (S > 0) {
+      CU(smp.ensure(S)); CU(ta.ensure(S)); CU(sray.ensure(S)); CU(dbg.ensure(S * 8));
+      k_emit<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p, offs.p, smp.p, ta.p, sray.p, dbg.p, (long long)S);
+      CU(cudaGetLastError());
+      CU(cudaMemcpyAsync(samples, dbg.p, (size_t)S * 32, cudaMemcpyDeviceToHost, D.stream));
+      CU(cudaStreamSynchronize(D.stream));
+    }
+  }
+  r.release(); smp.release(); f.release(); ta.release(); dbg.release(); cnt.release(); bs.release(); offs.release();
+  sray.release(); tot.release();
+  return rc;
+}
+
+static int upload_vec3_as_float4(Device& D, int n, const float* v3, DevBuf<float4>& out, float w = 0.f) {
+  std::vector<float4> h(n);
+  for (int i = 0; i < n; ++i) h[i] = make_float4(v3[i * 3], v3[i * 3 + 1], v3[i * 3 + 2], w);
+  CU(out.ensure(n));
+  CU(cudaMemcpyAsync(out.p, h.data(), (size_t)n * 16, cudaMemcpyHostToDevice, D.stream));
+  CU(cudaStreamSynchronize(D.stream));
+  return NRF_OK;
+}
+
+static void unpack_out(const std::vector<uint2>& h, float* out) {
+  for (size_t i = 0; i < h.size(); ++i) {
+    const uint32_t w[2] = {h[i].x, h[i].y};
+    for (int k = 0; k < 4; ++k) {
+      const uint16_t b = (uint16_t)(w[k >> 1] >> ((k & 1) * 16));
+      __half hh;
+      std::memcpy(&hh, &b, 2);
+      out[i * 4 + k] = __half2float(hh);
+    }
+  }
+}
+
+extern "C" int nrf_probe_encode(nrf_ctx* c, int n, const float* positions, uint16_t* enc_out, uint32_t* indices_out) {
+  NEED_MODEL(c);
+  if (n <= 0) return n == 0 ? NRF_OK : fail(NRF_EINVAL, "n < 0");
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  DevBuf<float4> pos;
+  int rc = upload_vec3_as_float4(D, n, positions, pos);
+  if (rc) return rc;
+  CU(D.enc.ensure((size_t)n * 4));
+  if (indices_out) CU(D.idx.ensure((size_t)n * NRF_L * 8));
+  CU(nrf_launch_network(0, std::max(1, std::min((n + 127) / 128, D.n_sms * 8)), D.stream, &D.net, n, pos.p, nullptr,
+                        nullptr, 1, D.enc.p, nullptr, indices_out ? D.idx.p : nullptr));
+  CU(cudaMemcpyAsync(enc_out, D.enc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, D.stream));
+  if (indices_out) CU(cudaMemcpyAsync(indices_out, D.idx.p, (size_t)n * NRF_L * 8 * 4, cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaStreamSynchronize(D.stream));
+  pos.release();
+  return NRF_OK;
+}
+
+extern "C" int nrf_probe_network(nrf_ctx* c, int n, const uint16_t* enc, const float* dirs, float* out, int impl) {
+  NEED_MODEL(c);
+  if (n <= 0) return n == 0 ? NRF_OK : fail(NRF_EINVAL, "n < 0");
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  DevBuf<float4> d4; DevBuf<uint2> o;
+  int rc = upload_vec3_as_float4(D, n, dirs, d4);
+  if (rc) return rc;
+  CU(D.enc.ensure((size_t)n * 4)); CU(o.ensure(n));
+  CU(cudaMemcpyAsync(D.enc.p, enc, (size_t)n * 64, cudaMemcpyHostToDevice, D.stream));
+  if (impl == 1) CU(nrf_launch_network_simt(D.stream, &D.net, n, D.enc.p, d4.p, o.p));
+  else CU(nrf_launch_network(1, network_grid(c, D, n), D.stream, &D.net, n, nullptr, nullptr, d4.p, 1, D.enc.p, o.p, nullptr));
+  std::vector<uint2> h(n);
+  CU(cudaMemcpyAsync(h.data(), o.p, (size_t)n * 8, cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaStreamSynchronize(D.stream));
+  unpack_out(h, out);
+  d4.release(); o.release();
+  return NRF_OK;
+}
+
+extern "C" int nrf_probe_samples(nrf_ctx* c, int n, const float* positions, const float* dirs, float* out) {
+  NEED_MODEL(c);
+  if (n <= 0) return n == 0 ? NRF_OK : fail(NRF_EINVAL, "n < 0");
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  DevBuf<float4> p4, d4; DevBuf<uint2> o;
+  int rc = upload_vec3_as_float4(D, n, positions, p4);
+  if (!rc) rc = upload_vec3_as_float4(D, n, dirs, d4);
+  if (rc) return rc;
+  CU(o.ensure(n));
+  CU(nrf_launch_network(2, network_grid(c, D, n), D.stream, &D.net, n, p4.p, nullptr, d4.p, 1, nullptr, o.p, nullptr));
+  std::vector<uint2> h(n);
+  CU(cudaMemcpyAsync(h.data(), o.p, (size_t)n * 8, cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaStreamSynchronize(D.stream));
+  unpack_out(h, out);
+  p4.release(); d4.release(); o.release();
+  return NRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- stage bench
+// Device-resident stage timing on the samples of the LAST rendered frame (so the access pattern is the real one):
+// what 0 = hash-grid gather only, 1 = MLP only (reads the encoded features), 2 = fused.  CUDA events on the launching
+// stream; between iterations nothing else touches L2 than the stage itself (the sample stream is >> L2 at full size).
+extern "C" int nrf_bench_stage(nrf_ctx* c, int what, int n, int iters, float* ms_out) {
+  NEED_MODEL(c);
+  if (!ms_out || iters < 1 || what < 0 || what > 2) return fail(NRF_EINVAL, "nrf_bench_stage: bad arguments");
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  const int S = (int)std::min<unsigned long long>(D.last_samples, n > 0 ? (unsigned long long)n : ~0ull);
+  if (S <= 0) return fail(NRF_ESTATE, "render a frame first (the stage bench replays its samples)");
+  CU(D.enc.ensure((size_t)S * 4));
+  const int grid = network_grid(c, D, S);
+  if (what == 1)  // produce the features once
+    CU(nrf_launch_network(0, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, 0, D.enc.p, nullptr, nullptr));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+  CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, 0, D.enc.p, D.sample_out.p, nullptr));
+  CU(cudaEventRecord(e0, D.stream));
+  for (int i = 0; i < iters; ++i)
+    CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, 0, D.enc.p, D.sample_out.p, nullptr));
+  CU(cudaEventRecord(e1, D.stream));
+  CU(cudaEventSynchronize(e1));
+  float ms = 0;
+  CU(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  *ms_out = ms / iters;
+  return NRF_OK;
+}

@@ -1,0 +1,185 @@
+"""Parity tests proper (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle on the same seeded
+inputs.  Bars (BASELINE.json north_star): rays / traversal / sample counts / hash indices / fp16 features BIT-EXACT;
+per-sample sigma and rgb within 1e-2 relative (fp16 MLP); images max abs <= 2/255 and PSNR >= 45 dB."""
+import numpy as np
+import pytest
+
+from nerf_cuda_b200 import NerfRender, synthetic as syn
+from oracle import orc
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-2          # per-sample sigma / rgb, relative (north_star)
+IMG_TOL = 2.0 / 255.0   # image max abs (north_star)
+PSNR_MIN = 45.0
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+@pytest.fixture(scope="module", params=["tiny", "tiny16"])
+def pair(request, built_lib):
+    sc = syn.make_scene(request.param)
+    r = NerfRender(1)
+    r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
+    yield request.param, sc, r, O
+    r.close()
+
+
+def rel_err(a, b):
+    return np.abs(a - b) / np.maximum(np.abs(b), 1e-2)
+
+
+def test_level_table_matches_oracle(pair):
+    from nerf_cuda_b200 import level_table
+    _, sc, _, O = pair
+    offs, scl, res = level_table(sc.desc)
+    o2, s2, r2, _ = O.level_table()
+    assert np.array_equal(offs, o2) and np.array_equal(bits(scl), bits(s2)) and np.array_equal(res, r2)
+
+
+@pytest.mark.parametrize("az", [0.0, 77.0, 201.0])
+def test_rays_bit_exact(pair, az):
+    name, sc, r, O = pair
+    W, H = 96, 64
+    intr, pose = syn.intrinsics(W, H), syn.look_at_pose(syn.camera_radius(name), 20.0, az)
+    o, d, nr, fr = r.probe_rays(intr, pose, W, H)
+    o2, d2, nr2, fr2 = O.rays(intr, pose, W, H)
+    assert np.array_equal(bits(o), bits(o2))
+    assert np.array_equal(bits(d), bits(d2))
+    assert np.array_equal(bits(nr), bits(nr2)) and np.array_equal(bits(fr), bits(fr2))
+
+
+def test_rays_miss_and_offset_window(pair):
+    name, sc, r, O = pair
+    W, H = 64, 64
+    intr = syn.intrinsics(W, H, fov_deg=120.0)  # wide: many rays miss the box when the camera is outside
+    pose = syn.look_at_pose(syn.camera_radius(name) * 3.0, 5.0, 10.0)
+    o, d, nr, fr = r.probe_rays(intr, pose, W, H, pix0=1000, n=777)
+    o2, d2, nr2, fr2 = O.rays(intr, pose, W, H, pix0=1000, n=777)
+    assert np.array_equal(bits(d), bits(d2)) and np.array_equal(bits(nr), bits(nr2)) and np.array_equal(bits(fr), bits(fr2))
+
+
+def test_march_bit_exact(pair):
+    name, sc, r, O = pair
+    W, H = 80, 60
+    intr, pose = syn.intrinsics(W, H), syn.look_at_pose(syn.camera_radius(name), 20.0, 33.0)
+    o, d, nr, fr = O.rays(intr, pose, W, H)
+    counts, samples = r.probe_march(o, d, nr, fr)
+    c2, s2 = O.march(o, d, nr, fr)
+    assert np.array_equal(counts, c2)          # sample counts bit-exact
+    assert counts.sum() > 0
+    assert np.array_equal(bits(samples), bits(s2))  # x,y,z,dt,t_after,level,cell,ray
+
+
+def test_march_empty_and_ragged(pair):
+    name, sc, r, O = pair
+    o = np.array([0.0, 0.0, -3.0 * sc.desc.bound], np.float32)
+    d = np.array([[0, 0, 1], [0, 1, 0], [0.6, 0.0, 0.8], [1e-8, 1e-8, 1.0]], np.float32)
+    nr = np.array([2.0 * sc.desc.bound, 3.4e38, 0.2, 0.2], np.float32)
+    fr = np.array([4.0 * sc.desc.bound, 3.4e38, 0.2, 5.0 * sc.desc.bound], np.float32)
+    counts, samples = r.probe_march(o, d, nr, fr)
+    c2, s2 = O.march(o, d, nr, fr)
+    assert np.array_equal(counts, c2) and np.array_equal(bits(samples), bits(s2))
+    c0, _ = r.probe_march(o, d[:0], nr[:0], fr[:0], want_samples=False)
+    assert c0.size == 0
+
+
+def test_encode_bit_exact(pair):
+    _, sc, r, O = pair
+    rng = np.random.default_rng(5)
+    pos = rng.random((20000, 3), dtype=np.float32)
+    pos[:8] = [[0, 0, 0], [1, 1, 1], [0.5, 0.5, 0.5], [1, 0, 0], [0, 1, 0], [0, 0, 1], [0.999999, 0.5, 0.25], [1e-7, 0.3, 0.7]]
+    enc, idx = r.probe_encode(pos, want_indices=True)
+    enc2, idx2 = O.encode(pos, want_indices=True)
+    assert np.array_equal(idx, idx2)   # hash indices bit-exact
+    assert np.array_equal(enc, enc2)   # fp16 features bit-exact (fp16 accumulation order replicated)
+
+
+def test_encode_ragged_sizes(pair):
+    _, sc, r, O = pair
+    rng = np.random.default_rng(6)
+    for n in (1, 127, 128, 129, 1000):
+        pos = rng.random((n, 3), dtype=np.float32)
+        assert np.array_equal(r.probe_encode(pos), O.encode(pos))
+
+
+@pytest.mark.parametrize("impl", [1, 0])
+def test_network_within_tolerance(pair, impl):
+    _, sc, r, O = pair
+    rng = np.random.default_rng(7)
+    n = 5000
+    pos = rng.random((n, 3), dtype=np.float32)
+    dirs = rng.normal(size=(n, 3)).astype(np.float32)
+    dirs = (dirs / np.linalg.norm(dirs, axis=1, keepdims=True) * 0.5 + 0.5).astype(np.float32)
+    enc = O.encode(pos)
+    ref = O.network(enc, dirs)
+    out = r.probe_network(enc, dirs, impl=impl)
+    assert np.isfinite(out).all()
+    err = rel_err(out, ref)
+    assert err.max() <= REL_TOL, f"impl={impl} max rel err {err.max()} at {np.unravel_index(err.argmax(), err.shape)}"
+
+
+def test_fused_samples_within_tolerance(pair):
+    _, sc, r, O = pair
+    rng = np.random.default_rng(8)
+    for n in (1, 130, 4099):
+        pos = rng.random((n, 3), dtype=np.float32)
+        dirs = rng.random((n, 3), dtype=np.float32)
+        ref = O.samples(pos, dirs)
+        out = r.probe_samples(pos, dirs)
+        assert rel_err(out, ref).max() <= REL_TOL
+
+
+def psnr(a, b):
+    mse = float(np.mean((a.astype(np.float64) - b.astype(np.float64)) ** 2))
+    return 99.0 if mse == 0 else 10.0 * np.log10(1.0 / mse)
+
+
+@pytest.mark.parametrize("az", [30.0, 250.0])
+def test_frame_parity(pair, az):
+    name, sc, r, O = pair
+    W, H = 100, 80
+    intr, pose = syn.intrinsics(W, H), syn.look_at_pose(syn.camera_radius(name), 20.0, az)
+    r.set_resolution((W, H))
+    rgb_u8, dep_u8 = r.render_frame(intr, pose)
+    rgb, dep, cnt = r.float_frame()
+    rgb2, dep2, cnt2 = O.render(intr, pose, W, H)
+    assert np.array_equal(cnt, cnt2)                       # composited sample counts bit-exact
+    assert np.abs(rgb - rgb2).max() <= IMG_TOL
+    assert psnr(np.clip(rgb, 0, 1), np.clip(rgb2, 0, 1)) >= PSNR_MIN
+    assert np.abs(dep - dep2).max() <= 1e-3
+    u8_ref = O.to_u8(rgb2).reshape(H, W, 3)
+    assert np.abs(rgb_u8.astype(int) - u8_ref.astype(int)).max() <= 2
+    assert rgb_u8.shape == (H, W, 3) and dep_u8.shape == (H, W)
+    st = r.stats()
+    assert st.n_samples == cnt2.sum() or st.n_samples >= cnt2.sum()
+
+
+def test_frame_sigmoid_activation(built_lib):
+    sc = syn.make_scene("tiny", rgb_activation=syn.NRF_ACT_SIGMOID)
+    r = NerfRender(1)
+    r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
+    W, H = 64, 48
+    intr, pose = syn.intrinsics(W, H), syn.look_at_pose(4.0, 20.0, 10.0)
+    r.set_resolution((W, H))
+    r.render_frame(intr, pose)
+    rgb, dep, cnt = r.float_frame()
+    rgb2, dep2, cnt2 = O.render(intr, pose, W, H)
+    assert np.array_equal(cnt, cnt2) and np.abs(rgb - rgb2).max() <= IMG_TOL
+    r.close()
+
+
+def test_set_resolution_idempotent_and_resize(pair):
+    name, sc, r, O = pair
+    intr, pose = syn.intrinsics(32, 32), syn.look_at_pose(syn.camera_radius(name), 20.0, 0.0)
+    r.set_resolution((32, 32)); r.set_resolution((32, 32))
+    a, _ = r.render_frame(intr, pose)
+    a = a.copy()
+    r.set_resolution((48, 16))
+    r.set_resolution((32, 32))
+    b, _ = r.render_frame(intr, pose)
+    assert np.array_equal(a, b)   # idempotent + deterministic
