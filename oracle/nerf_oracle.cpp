@@ -278,16 +278,31 @@ void sh4(const float in[3], uint16_t out[16]) {
 // ---- MLP: tcnn/src/fully_fused_mlp.cu:316-558 (inference), weights row-major [out][in] (:662-686,874-883),
 //      wiring nerf_network.h:148-196, activation common_device.h:68-114 ------------------------------------
 struct Mlp {
-  const uint16_t *W0, *W1, *V0, *V1, *V2;  // fp16 bit patterns
+  // weights converted to float once and transposed to [in][out] so the per-output fp32 accumulation (k ascending,
+  // identical order to a row-major dot product) vectorises across outputs
+  std::vector<float> Wt[5];
 };
-inline Mlp mlp_view(const uint16_t* w) { return {w, w + 2048, w + 3072, w + 5120, w + 9216}; }
+inline Mlp mlp_view(const uint16_t* w) {
+  static const int offs[5] = {0, 2048, 3072, 5120, 9216}, n_out[5] = {64, 16, 64, 64, 16}, n_in[5] = {32, 64, 32, 64, 64};
+  Mlp m;
+  for (int l = 0; l < 5; ++l) {
+    m.Wt[l].resize((size_t)n_out[l] * n_in[l]);
+    for (int o = 0; o < n_out[l]; ++o)
+      for (int k = 0; k < n_in[l]; ++k) m.Wt[l][(size_t)k * n_out[l] + o] = h2f(bits2h(w[offs[l] + o * n_in[l] + k]));
+  }
+  return m;
+}
 
-inline void dense(const uint16_t* W, int n_out, int n_in, const half_t* x, half_t* y, bool relu) {
+inline void dense(const std::vector<float>& Wt, int n_out, int n_in, const half_t* x, half_t* y, bool relu) {
+  float acc[64];
+  for (int o = 0; o < n_out; ++o) acc[o] = 0.f;
+  for (int k = 0; k < n_in; ++k) {
+    const float xk = h2f(x[k]);
+    const float* row = Wt.data() + (size_t)k * n_out;
+    for (int o = 0; o < n_out; ++o) acc[o] += row[o] * xk;
+  }
   for (int o = 0; o < n_out; ++o) {
-    float acc = 0.f;
-    const uint16_t* row = W + (size_t)o * n_in;
-    for (int k = 0; k < n_in; ++k) acc += h2f(bits2h(row[k])) * h2f(x[k]);
-    half_t h = f2h(acc);
+    half_t h = f2h(acc[o]);
     if (relu) h = (h2f(h) > 0.0f) ? h : f2h(0.0f) * h;  // x * (x > 0): keeps -0 for negatives like the reference
     y[o] = h;
   }
@@ -308,12 +323,12 @@ inline half_t act_out(uint32_t act, half_t v) {  // warp_activation / wrap_a_act
 void network_sample(const nrf_model_desc& d, const Mlp& m, const uint16_t* enc, const uint16_t* sh, float out[4]) {
   half_t x[32], h[64], den[16], rin[32], h1[64], h2[64], rgb[16];
   for (int k = 0; k < 32; ++k) x[k] = bits2h(enc[k]);
-  dense(m.W0, 64, 32, x, h, true);
-  dense(m.W1, 16, 64, h, den, false);
+  dense(m.Wt[0], 64, 32, x, h, true);
+  dense(m.Wt[1], 16, 64, h, den, false);
   for (int k = 0; k < 16; ++k) { rin[k] = den[k]; rin[16 + k] = bits2h(sh[k]); }
-  dense(m.V0, 64, 32, rin, h1, true);
-  dense(m.V1, 64, 64, h1, h2, true);
-  dense(m.V2, 16, 64, h2, rgb, false);
+  dense(m.Wt[2], 64, 32, rin, h1, true);
+  dense(m.Wt[3], 64, 64, h1, h2, true);
+  dense(m.Wt[4], 16, 64, h2, rgb, false);
   for (int k = 0; k < 3; ++k) out[k] = h2f(act_out(d.rgb_activation, rgb[k]));
   out[3] = h2f(act_out(d.sigma_activation, den[0]));  // extract_density, nerf_network.h:49-61,187-195
 }
