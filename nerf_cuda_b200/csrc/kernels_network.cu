@@ -126,9 +126,26 @@ __device__ __forceinline__ uint32_t encode_level(const LevelInfo& lv, const __ha
   uint32_t e[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) e[k] = grid_entry(lv, g0 + (k & 1), g1 + ((k >> 1) & 1), g2 + ((k >> 2) & 1));
+  // The two x-corners of a cell are adjacent entries whenever x is even (hash prime for x is 1, grid.h:88; dense rows
+  // are contiguous): one aligned 8-byte load then serves both corners and costs the L1 a single sector request
+  // instead of two.  Values and accumulation order are unchanged.
   __half2 v[8];
+  const uint32_t* tab32 = reinterpret_cast<const uint32_t*>(tab);
 #pragma unroll
-  for (int k = 0; k < 8; ++k) v[k] = __ldg(tab + e[k]);
+  for (int k = 0; k < 8; k += 2) {
+    const uint32_t ea = e[k], eb = e[k + 1];
+    uint32_t ra, rb;
+    if ((ea ^ eb) == 1u) {
+      const uint2 q = __ldg(reinterpret_cast<const uint2*>(tab32 + (ea & ~1u)));
+      ra = (ea & 1u) ? q.y : q.x;
+      rb = (ea & 1u) ? q.x : q.y;
+    } else {
+      ra = __ldg(tab32 + ea);
+      rb = __ldg(tab32 + eb);
+    }
+    v[k] = *reinterpret_cast<__half2*>(&ra);
+    v[k + 1] = *reinterpret_cast<__half2*>(&rb);
+  }
   if (idx_out) {
 #pragma unroll
     for (int k = 0; k < 8; ++k) idx_out[k] = e[k];
@@ -391,17 +408,28 @@ k_network_simt(const __grid_constant__ NetParams P, int n, const uint4* __restri
 // ------------------------------------------------------------------------------------------------ host launchers
 extern "C" size_t nrf_network_smem_bytes() { return SMEM_W_BYTES + SMEM_A_BYTES + 64; }
 
+static void nrf_network_setup() {
+  static bool attr_set = false;
+  if (attr_set) return;
+  const size_t smem = nrf_network_smem_bytes();
+  {
+    cudaFuncSetAttribute(k_network<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_network<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_network<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // ask for the full shared-memory carveout: several 37 KB CTAs per SM must be resident to overlap one tile's
+    // gather with another tile's MLP (the occupancy query reports 1 CTA/SM under the default carveout)
+    cudaFuncSetAttribute(k_network<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(k_network<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(k_network<2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    attr_set = true;
+  }
+}
+
 extern "C" cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t stream, const NetParams* P, int n,
                                           const float4* samples, const int* sample_ray, const float4* rays,
                                           int dirs_mode, uint4* enc_io, uint2* out, uint32_t* idx_out) {
   const size_t smem = nrf_network_smem_bytes();
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(k_network<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaFuncSetAttribute(k_network<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaFuncSetAttribute(k_network<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr_set = true;
-  }
+  nrf_network_setup();
   if (n <= 0) return cudaSuccess;
   switch (mode) {
     case 0: k_network<0><<<grid, NET_THREADS, smem, stream>>>(*P, n, samples, sample_ray, rays, dirs_mode, enc_io, out, idx_out); break;
@@ -419,10 +447,16 @@ extern "C" cudaError_t nrf_launch_network_simt(cudaStream_t stream, const NetPar
 }
 
 extern "C" int nrf_network_occupancy(int mode) {
+  nrf_network_setup();
   int nb = 0;
   const size_t smem = nrf_network_smem_bytes();
-  if (mode == 0) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_network<0>, NET_THREADS, smem);
-  else if (mode == 1) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_network<1>, NET_THREADS, smem);
-  else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_network<2>, NET_THREADS, smem);
+  cudaError_t e;
+  if (mode == 0) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_network<0>, NET_THREADS, smem);
+  else if (mode == 1) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_network<1>, NET_THREADS, smem);
+  else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_network<2>, NET_THREADS, smem);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return -(int)e;
+  }
   return nb;
 }

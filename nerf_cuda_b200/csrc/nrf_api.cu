@@ -15,6 +15,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <string>
@@ -487,7 +488,14 @@ static void set_pose(nrf_ctx* c, MarchParams& M, const float intr[4], const floa
 }
 
 static int network_grid(nrf_ctx* c, const Device& D, int n_samples) {
-  if (!c->net_grid_ctas_per_sm) c->net_grid_ctas_per_sm = std::max(1, nrf_network_occupancy(2));
+  if (!c->net_grid_ctas_per_sm) {
+    // Resident CTAs per SM: limits are shared memory 227 KB / 36.9 KB = 6, registers 65536 / (128*72) = 7, TMEM
+    // 512 / 64 columns = 8.  (cudaOccupancyMaxActiveBlocksPerMultiprocessor reports 1 for this kernel on the
+    // 580.159 driver although 4-8 CTAs are measurably co-resident.)  Measured best on B200: 4 (profiles/).
+    int occ = 4;
+    if (const char* env = std::getenv("NRF_NET_CTAS_PER_SM")) occ = std::atoi(env);
+    c->net_grid_ctas_per_sm = std::min(std::max(occ, 1), 8);
+  }
   const int tiles = (n_samples + NRF_TILE - 1) / NRF_TILE;
   return std::max(1, std::min(tiles, D.n_sms * c->net_grid_ctas_per_sm));
 }
