@@ -107,60 +107,68 @@ __device__ __forceinline__ __half act_h(uint32_t act, __half v) {
   }
 }
 
-// tcnn grid_index (grid.h:100-117) for one corner.  Dense levels: x + y*res + z*res^2 (< 2*T, so one conditional
-// subtract == the reference's `% T`); hashed levels: T is a power of two.
-__device__ __forceinline__ uint32_t grid_entry(const LevelInfo& lv, uint32_t x, uint32_t y, uint32_t z) {
-  if (lv.hashed) return (x ^ (y * 2654435761u) ^ (z * 805459861u)) & (lv.size - 1u);
-  uint32_t idx = x + y * lv.res + z * lv.res * lv.res;
-  return idx >= lv.size ? idx - lv.size : idx;
-}
-
-// One level of tcnn kernel_grid (grid.h:186-268): trilinear blend accumulated in fp16 in corner order 0..7.
+// One level of tcnn kernel_grid (grid.h:186-268) + grid_index/fast_hash (grid.h:81-117): trilinear blend accumulated
+// in fp16 in corner order 0..7 (corner bit d selects g[d]+1 and weight w[d], else 1-w[d]; weight = (f0*f1)*f2).
+// Index math: hashed levels  (x ^ y*2654435761 ^ z*805459861) & (T-1)   (T is a power of two);
+//             dense levels   x + y*res + z*res^2, which is < 2T, so one conditional subtract equals the reference's % T.
+// The two x-corners of a cell are adjacent entries whenever they fall in the same aligned 8-byte slot (always when x is
+// even on hashed levels — the hash prime for x is 1, grid.h:88 — and for even base indices on dense levels): one
+// 8-byte load then serves both corners and costs the L1 a single sector request.  Values and order are unchanged.
 __device__ __forceinline__ uint32_t encode_level(const LevelInfo& lv, const __half2* __restrict__ table, float u0,
                                                  float u1, float u2, uint32_t* idx_out) {
   const float p0 = u0 * lv.scale + 0.5f, p1 = u1 * lv.scale + 0.5f, p2 = u2 * lv.scale + 0.5f;  // -fmad=false
   const float f0 = floorf(p0), f1 = floorf(p1), f2 = floorf(p2);
   const uint32_t g0 = (uint32_t)(int)f0, g1 = (uint32_t)(int)f1, g2 = (uint32_t)(int)f2;
   const float w0 = p0 - f0, w1 = p1 - f1, w2 = p2 - f2;
-  const __half2* tab = table + lv.offset;
+  const float o0 = 1.0f - w0, o1 = 1.0f - w1, o2 = 1.0f - w2;
+  const float wxy[4] = {o0 * o1, w0 * o1, o0 * w1, w0 * w1};  // (f0 * f1), corner bits 0,1
+  const uint32_t* tab32 = reinterpret_cast<const uint32_t*>(table + lv.offset);
   uint32_t e[8];
+  if (lv.hashed) {
+    const uint32_t m = lv.size - 1u;
+    const uint32_t hy0 = g1 * 2654435761u, hy1 = hy0 + 2654435761u, hz0 = g2 * 805459861u, hz1 = hz0 + 805459861u;
+    const uint32_t yz[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
 #pragma unroll
-  for (int k = 0; k < 8; ++k) e[k] = grid_entry(lv, g0 + (k & 1), g1 + ((k >> 1) & 1), g2 + ((k >> 2) & 1));
-  // The two x-corners of a cell are adjacent entries whenever x is even (hash prime for x is 1, grid.h:88; dense rows
-  // are contiguous): one aligned 8-byte load then serves both corners and costs the L1 a single sector request
-  // instead of two.  Values and accumulation order are unchanged.
-  __half2 v[8];
-  const uint32_t* tab32 = reinterpret_cast<const uint32_t*>(tab);
+    for (int j = 0; j < 4; ++j) {
+      e[2 * j] = (g0 ^ yz[j]) & m;
+      e[2 * j + 1] = ((g0 + 1u) ^ yz[j]) & m;
+    }
+  } else {
+    const uint32_t r1 = lv.res, r2 = lv.res * lv.res, T = lv.size;
+    const uint32_t b = g0 + g1 * r1 + g2 * r2;
+    const uint32_t off[4] = {0u, r1, r2, r1 + r2};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      uint32_t a = b + off[j], c = a + 1u;
+      e[2 * j] = a >= T ? a - T : a;
+      e[2 * j + 1] = c >= T ? c - T : c;
+    }
+  }
+  uint32_t raw[8];
 #pragma unroll
   for (int k = 0; k < 8; k += 2) {
     const uint32_t ea = e[k], eb = e[k + 1];
-    uint32_t ra, rb;
     if ((ea ^ eb) == 1u) {
       const uint2 q = __ldg(reinterpret_cast<const uint2*>(tab32 + (ea & ~1u)));
-      ra = (ea & 1u) ? q.y : q.x;
-      rb = (ea & 1u) ? q.x : q.y;
+      raw[k] = (ea & 1u) ? q.y : q.x;
+      raw[k + 1] = (ea & 1u) ? q.x : q.y;
     } else {
-      ra = __ldg(tab32 + ea);
-      rb = __ldg(tab32 + eb);
+      raw[k] = __ldg(tab32 + ea);
+      raw[k + 1] = __ldg(tab32 + eb);
     }
-    v[k] = *reinterpret_cast<__half2*>(&ra);
-    v[k + 1] = *reinterpret_cast<__half2*>(&rb);
   }
   if (idx_out) {
 #pragma unroll
     for (int k = 0; k < 8; ++k) idx_out[k] = e[k];
   }
-  __half a0 = __float2half_rn(0.f), a1 = __float2half_rn(0.f);
+  __half2 acc = __floats2half2_rn(0.f, 0.f);
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    float weight = 1.0f;
-    weight *= (k & 1) ? w0 : 1.0f - w0;
-    weight *= (k & 2) ? w1 : 1.0f - w1;
-    weight *= (k & 4) ? w2 : 1.0f - w2;
-    a0 = __hadd(a0, __float2half_rn(weight * __low2float(v[k])));
-    a1 = __hadd(a1, __float2half_rn(weight * __high2float(v[k])));
+    const float weight = wxy[k & 3] * ((k & 4) ? w2 : o2);
+    const float2 v = __half22float2(*reinterpret_cast<const __half2*>(&raw[k]));
+    acc = __hadd2(acc, __floats2half2_rn(weight * v.x, weight * v.y));  // per-component fp16 RN add, as __half +=
   }
-  return pack_h2(a0, a1);
+  return *reinterpret_cast<uint32_t*>(&acc);
 }
 
 // tcnn kernel_sh degree 4 (spherical_harmonics.h:66-96); in = normalised direction input in [0,1]
@@ -199,14 +207,19 @@ __device__ __forceinline__ void load_acc(uint32_t taddr, uint32_t* acc) {
 // ReLU -> fp16 -> this row's K-major chunks of the A tile: chunk kc (8 halves) lives at kc*2048 + row*16.
 template <int NCOLS>
 __device__ __forceinline__ void store_relu_row(uint8_t* sA, int row, const uint32_t* acc) {
+  // ReLU then fp16 RN.  tcnn computes half(x) * (half(x) > 0) (common_device.h:71-76); max(x,0) then rounding gives
+  // the same value for every finite x (rounding is monotonic and keeps the sign), except that a negative input yields
+  // +0 instead of -0, which is indistinguishable as an MMA operand.
 #pragma unroll
   for (int kc = 0; kc < NCOLS / 8; ++kc) {
-    uint4 v;
-    v.x = pack_h2(relu_h(__uint_as_float(acc[kc * 8 + 0])), relu_h(__uint_as_float(acc[kc * 8 + 1])));
-    v.y = pack_h2(relu_h(__uint_as_float(acc[kc * 8 + 2])), relu_h(__uint_as_float(acc[kc * 8 + 3])));
-    v.z = pack_h2(relu_h(__uint_as_float(acc[kc * 8 + 4])), relu_h(__uint_as_float(acc[kc * 8 + 5])));
-    v.w = pack_h2(relu_h(__uint_as_float(acc[kc * 8 + 6])), relu_h(__uint_as_float(acc[kc * 8 + 7])));
-    *reinterpret_cast<uint4*>(sA + kc * (NRF_TILE * 16) + row * 16) = v;
+    uint32_t w[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const __half2 h = __floats2half2_rn(fmaxf(__uint_as_float(acc[kc * 8 + 2 * j]), 0.f),
+                                          fmaxf(__uint_as_float(acc[kc * 8 + 2 * j + 1]), 0.f));
+      w[j] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    *reinterpret_cast<uint4*>(sA + kc * (NRF_TILE * 16) + row * 16) = make_uint4(w[0], w[1], w[2], w[3]);
   }
 }
 
@@ -253,14 +266,16 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     const int i = tile * NRF_TILE + tid;
     const bool valid = i < n;
     // ---- stage A0: 32 encoded features of this thread's sample ---------------------------------------------------
-    uint4 a0[4];
+    // (the A tile is free here: the previous tile's last MMA was waited on and its TMEM reads are fenced below)
     if (MODE == 1) {
 #pragma unroll
-      for (int kc = 0; kc < 4; ++kc) a0[kc] = valid ? __ldg(enc_io + (size_t)i * 4 + kc) : make_uint4(0, 0, 0, 0);
+      for (int kc = 0; kc < 4; ++kc)
+        *reinterpret_cast<uint4*>(sA + kc * (NRF_TILE * 16) + tid * 16) =
+            valid ? __ldg(enc_io + (size_t)i * 4 + kc) : make_uint4(0, 0, 0, 0);
     } else {
-      float4 s = valid ? __ldg(samples + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-      for (int kc = 0; kc < 4; ++kc) {
+      const float4 s = valid ? __ldg(samples + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+      for (int kc = 0; kc < 4; ++kc) {  // rolled: keeps the gather body (4 levels) resident in the instruction cache
         uint32_t f[4];
 #pragma unroll
         for (int li = 0; li < 4; ++li) {
@@ -268,16 +283,15 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
           f[li] = encode_level(P.lv[l], P.table, s.x, s.y, s.z,
                                (idx_out && valid) ? idx_out + ((size_t)i * NRF_L + l) * 8 : nullptr);
         }
-        a0[kc] = make_uint4(f[0], f[1], f[2], f[3]);
+        const uint4 v = make_uint4(f[0], f[1], f[2], f[3]);
+        if (MODE == 0) {
+          if (valid) enc_io[(size_t)i * 4 + kc] = v;
+        } else {
+          *reinterpret_cast<uint4*>(sA + kc * (NRF_TILE * 16) + tid * 16) = v;
+        }
       }
     }
-    if (MODE == 0) {
-      if (valid) {
-#pragma unroll
-        for (int kc = 0; kc < 4; ++kc) enc_io[(size_t)i * 4 + kc] = a0[kc];
-      }
-      continue;
-    }
+    if (MODE == 0) continue;
     // ---- direction -> SH (per sample here; the direction is per ray) ---------------------------------------------
     uint32_t sh[8];
     {
@@ -293,8 +307,6 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
       }
       sh4(dx, dy, dz, sh);
     }
-#pragma unroll
-    for (int kc = 0; kc < 4; ++kc) *reinterpret_cast<uint4*>(sA + kc * (NRF_TILE * 16) + tid * 16) = a0[kc];
     fence_proxy_async();
     __syncthreads();
 

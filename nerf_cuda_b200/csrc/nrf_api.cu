@@ -857,3 +857,28 @@ extern "C" int nrf_bench_stage(nrf_ctx* c, int what, int n, int iters, float* ms
   *ms_out = ms / iters;
   return NRF_OK;
 }
+
+// Experiment hook (not part of the public header): time the gather stage on caller-supplied positions.
+extern "C" int nrf_bench_encode_positions(nrf_ctx* c, int n, const float* positions, int iters, float* ms_out) {
+  NEED_MODEL(c);
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  DevBuf<float4> pos;
+  int rc = upload_vec3_as_float4(D, n, positions, pos);
+  if (rc) return rc;
+  CU(D.enc.ensure((size_t)n * 4));
+  const int grid = network_grid(c, D, n);
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+  CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr));
+  CU(cudaEventRecord(e0, D.stream));
+  for (int i = 0; i < iters; ++i)
+    CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr));
+  CU(cudaEventRecord(e1, D.stream));
+  CU(cudaEventSynchronize(e1));
+  float ms = 0;
+  CU(cudaEventElapsedTime(&ms, e0, e1));
+  *ms_out = ms / iters;
+  pos.release();
+  return NRF_OK;
+}
