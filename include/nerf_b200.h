@@ -102,6 +102,11 @@ int nrf_load_snapshot(nrf_ctx* ctx, const char* path);
 int nrf_load_raw(nrf_ctx* ctx, const nrf_model_desc* desc, const float* params, size_t n_params,
                  const float* density_grid, size_t n_grid, const float aabb[6]);
 int nrf_get_model_desc(nrf_ctx* ctx, nrf_model_desc* out);
+/* Host-only: parse a snapshot file (load_snapshot, nerf_render.cu:431-473 + load_network_config :66-91) without
+ * touching a device; reports the model description, array lengths, aabb and (for integrity checks) the double-precision
+ * sums of the two arrays.  Any output pointer may be NULL.  Same error codes / messages as nrf_load_snapshot. */
+int nrf_snapshot_inspect(const char* path, nrf_model_desc* desc, uint64_t* n_params, uint64_t* n_grid, float aabb[6],
+                         double* params_sum, double* grid_sum);
 
 /* NerfRender::set_resolution (nerf_render.cu:186-236); idempotent here (reference defect D7). */
 int nrf_set_resolution(nrf_ctx* ctx, int width, int height);

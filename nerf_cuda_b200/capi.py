@@ -37,6 +37,7 @@ EXPORTS = [
     "nrf_render_batch", "nrf_render_frame_device", "nrf_get_float_frame", "nrf_get_stats", "nrf_synchronize",
     "nrf_probe_rays", "nrf_probe_march", "nrf_probe_encode", "nrf_probe_network", "nrf_probe_samples",
     "nrf_bench_stage", "nrf_set_shard", "nrf_local_rays", "nrf_device_outputs", "nrf_stream", "nrf_shard_pixel",
+    "nrf_snapshot_inspect",
 ]
 
 _lib = None

@@ -362,8 +362,8 @@ extern "C" int nrf_load_raw(nrf_ctx* c, const nrf_model_desc* desc, const float*
   return NRF_OK;
 }
 
-extern "C" int nrf_load_snapshot(nrf_ctx* c, const char* path) {
-  if (!c || !path) return fail(NRF_EINVAL, "nrf_load_snapshot: null argument");
+// Reads and parses a snapshot file on the host (no device needed).
+static int read_snapshot(const char* path, nrf::Snapshot& snap) {
   const std::string p(path);
   // reload_network_from_file accepts only .msgpack (nerf_render.cu:98,105-107)
   if (p.size() < 8 || p.substr(p.size() - 8) != ".msgpack")
@@ -377,14 +377,36 @@ extern "C" int nrf_load_snapshot(nrf_ctx* c, const char* path) {
   const size_t got = sz > 0 ? std::fread(buf.data(), 1, (size_t)sz, f) : 0;
   std::fclose(f);
   if ((long)got != sz) return fail(NRF_EIO, "short read on %s", path);
-  nrf::Snapshot snap;
   try {
     nrf::parse_snapshot(buf.data(), buf.size(), p, snap);
   } catch (const std::exception& e) {
     return fail(NRF_EFORMAT, "%s", e.what());
   }
+  return NRF_OK;
+}
+
+extern "C" int nrf_load_snapshot(nrf_ctx* c, const char* path) {
+  if (!c || !path) return fail(NRF_EINVAL, "nrf_load_snapshot: null argument");
+  nrf::Snapshot snap;
+  int rc = read_snapshot(path, snap);
+  if (rc) return rc;
   return nrf_load_raw(c, &snap.desc, snap.params.data(), snap.params.size(), snap.density_grid.data(),
                       snap.density_grid.size(), snap.aabb);
+}
+
+extern "C" int nrf_snapshot_inspect(const char* path, nrf_model_desc* desc, uint64_t* n_params, uint64_t* n_grid,
+                                    float aabb[6], double* params_sum, double* grid_sum) {
+  if (!path) return fail(NRF_EINVAL, "nrf_snapshot_inspect: null path");
+  nrf::Snapshot snap;
+  int rc = read_snapshot(path, snap);
+  if (rc) return rc;
+  if (desc) *desc = snap.desc;
+  if (n_params) *n_params = snap.params.size();
+  if (n_grid) *n_grid = snap.density_grid.size();
+  if (aabb) std::memcpy(aabb, snap.aabb, 24);
+  if (params_sum) { double s = 0; for (float v : snap.params) s += v; *params_sum = s; }
+  if (grid_sum) { double s = 0; for (float v : snap.density_grid) s += v; *grid_sum = s; }
+  return NRF_OK;
 }
 
 extern "C" int nrf_get_model_desc(nrf_ctx* c, nrf_model_desc* out) {
