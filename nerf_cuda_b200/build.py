@@ -9,7 +9,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libnerf_b200.so")
 SOURCES = ["nrf_api.cu", "kernels_exact.cu", "kernels_network.cu", "kernels_composite.cu"]
-HEADERS = ["nrf_device.cuh", "nrf_snapshot.h", "../../include/nerf_b200.h", "../../include/nerf_b200_ext.h"]
+HEADERS = ["nrf_device.cuh", "nrf_snapshot.h", "../../include/nerf_b200.h", "../../include/nerf_b200_ext.h",
+           "../../include/nerf-cuda/nerf_render.h", "../host/render_server.cpp", "../host/testbed.cpp"]
+# host executables (C++ over the C ABI): the reference's render_server / testbed counterparts
+HOST_EXES = {"render_server": "host/render_server.cpp", "testbed": "host/testbed.cpp"}
 # -fmad=false: the march / encode / SH expression trees are the reference's, evaluated without FMA contraction so
 # they are bit-exact against the oracle (DESIGN.md numerics contract).  Nothing on the path is FMA-throughput bound.
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
@@ -24,7 +27,7 @@ def _nvcc() -> str:
 
 
 def needs_build() -> bool:
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or not all(os.path.exists(os.path.join(HERE, e)) for e in HOST_EXES):
         return True
     t = os.path.getmtime(LIB)
     deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__)]
@@ -51,6 +54,13 @@ def build(force=False, verbose=False) -> str:
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
         raise RuntimeError("nvcc link failed")
+    for exe, src in HOST_EXES.items():
+        cmd = ["g++", "-std=c++17", "-O2", "-Wall", os.path.join(HERE, src), "-o", os.path.join(HERE, exe), "-L", HERE,
+               "-lnerf_b200", "-Wl,-rpath,$ORIGIN"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError(f"g++ failed on {src}")
     with open(os.path.join(HERE, "build", "ptxas.log"), "w") as f:
         f.write("\n".join(log))
     if verbose:
