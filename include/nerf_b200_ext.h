@@ -11,18 +11,22 @@
 extern "C" {
 #endif
 
-/* This context renders only pixel blocks b with b % n_shards == shard, block = `block_pixels` consecutive pixels in
- * row-major order (reference: pixel = NGPU*tid + gpu, render_utils.h:37, i.e. block_pixels = 1).  Call before
- * nrf_set_resolution.  Outputs of a sharded context are packed in local ray order. */
-int nrf_set_shard(nrf_ctx* ctx, int shard, int n_shards, int block_pixels);
-/* Number of rays this context renders per frame (after nrf_set_resolution). */
+/* This context renders only the 32x32-pixel image tiles t with t % n_shards == shard (tiles numbered row-major;
+ * reference: pixel = NGPU*tid + gpu, render_utils.h:37).  Call before nrf_set_resolution; the context must own exactly
+ * one device.  The u8 outputs of a sharded context are PACKED: its tiles in local order, 1024 pixels each, row-major
+ * inside the tile (pixels of an edge tile that fall outside the image are present and zero). */
+int nrf_set_shard(nrf_ctx* ctx, int shard, int n_shards);
+/* Number of ray slots this context renders per frame (after nrf_set_resolution): its tiles x 1024, including the
+ * out-of-image slots of edge tiles. */
 int nrf_local_rays(nrf_ctx* ctx, int* n_local);
-/* Device pointers of the last frame's packed outputs on device 0 of the context: rgb u8 [n_local*3],
- * depth u8 [n_local], rgb f32 [n_local*3].  Valid until nrf_set_resolution / nrf_destroy. */
+/* Device pointers of the last frame's outputs on device 0 of the context: rgb u8 / depth u8 (whole frame in pixel
+ * order for an unsharded context, packed tiles [n_local*3] / [n_local] for a sharded one) and rgb f32 [n_local*3] in
+ * local ray order.  Valid until nrf_set_resolution / nrf_destroy. */
 int nrf_device_outputs(nrf_ctx* ctx, void** rgb_u8, void** depth_u8, void** rgb_f32);
 /* CUDA stream (cudaStream_t) of device 0, for event timing on the launching stream. */
 int nrf_stream(nrf_ctx* ctx, void** stream);
-/* Global pixel index of local ray q (host arithmetic; same map the kernels use). */
+/* Global pixel index of local ray q, or -1 for a slot outside the image (host arithmetic; same map the kernels use:
+ * q = local_tile*1024 + patch*32 + lane, patches of 8x4 pixels, 4x8 patches per tile). */
 int nrf_shard_pixel(nrf_ctx* ctx, int q, int* pixel);
 
 #ifdef __cplusplus

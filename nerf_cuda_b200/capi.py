@@ -91,7 +91,7 @@ class NerfRender:
         ids = (C.c_int * n_gpus)(*device_ids) if device_ids is not None else None
         _check(self._l.nrf_create(n_gpus, ids, C.byref(self._ctx)))
         self.W = self.H = 0
-        self._shard = (1, 0, 1)
+        self._shard = (0, 1)   # (shard, n_shards)
 
     def close(self):
         if getattr(self, "_ctx", None) and self._ctx.value:
@@ -119,14 +119,14 @@ class NerfRender:
     def render_frame(self, cam, pos):
         """cam = (fl_x, fl_y, cx, cy) (struct Camera); pos = 4x4 camera-to-world (NeRF convention).
         Returns (rgb u8 [H,W,3], depth u8 [H,W]) views of context-owned pinned memory (struct Image semantics),
-        or packed local pixels [n_local,3] / [n_local] for a sharded context."""
+        or this shard's packed tiles [n_tiles,32,32,3] / [n_tiles,32,32] for a sharded context."""
         intr, pose = _f32(cam).reshape(4), _f32(pos).reshape(16)
         rgb, dep = C.POINTER(C.c_uint8)(), C.POINTER(C.c_uint8)()
         _check(self._l.nrf_render_frame(self._ctx, _p(intr, C.c_float), _p(pose, C.c_float), C.byref(rgb), C.byref(dep)))
-        n = self.local_rays()
-        if n == self.W * self.H:
+        if self._shard[1] == 1:
             return (np.ctypeslib.as_array(rgb, (self.H, self.W, 3)), np.ctypeslib.as_array(dep, (self.H, self.W)))
-        return np.ctypeslib.as_array(rgb, (n, 3)), np.ctypeslib.as_array(dep, (n,))
+        t = self.local_rays() // 1024
+        return np.ctypeslib.as_array(rgb, (t, 32, 32, 3)), np.ctypeslib.as_array(dep, (t, 32, 32))
 
     # ---- extensions -----------------------------------------------------------------------------------------------
     def render_frame_device(self, cam, pos):
@@ -135,14 +135,17 @@ class NerfRender:
 
     def render_batch(self, cam, poses):
         intr, poses = _f32(cam).reshape(4), _f32(poses).reshape(-1, 16)
-        n = self.local_rays()
+        whole = self._shard[1] == 1
+        n = self.W * self.H if whole else self.local_rays()
         out = np.zeros((poses.shape[0], n, 3), np.uint8)
         _check(self._l.nrf_render_batch(self._ctx, _p(intr, C.c_float), _p(poses, C.c_float), poses.shape[0],
                                         _p(out, C.c_uint8)))
-        return out.reshape(poses.shape[0], self.H, self.W, 3) if n == self.W * self.H else out
+        return out.reshape(poses.shape[0], self.H, self.W, 3) if whole else out.reshape(poses.shape[0], -1, 32, 32, 3)
 
     def float_frame(self):
-        n = self.local_rays()
+        """Float image of the last frame + composited samples per ray: global pixel order [W*H] for a whole-frame
+        context, packed tile order [n_local] for a sharded one."""
+        n = self.W * self.H if self._shard[1] == 1 else self.local_rays()
         rgb, dep, cnt = np.zeros((n, 3), np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32)
         _check(self._l.nrf_get_float_frame(self._ctx, _p(rgb, C.c_float), _p(dep, C.c_float), _p(cnt, C.c_int32)))
         return rgb, dep, cnt
@@ -155,9 +158,9 @@ class NerfRender:
         _check(self._l.nrf_get_stats(self._ctx, C.byref(s)))
         return s
 
-    def set_shard(self, shard, n_shards, block_pixels=1024):
-        _check(self._l.nrf_set_shard(self._ctx, shard, n_shards, block_pixels))
-        self._shard = (block_pixels, shard, n_shards)
+    def set_shard(self, shard, n_shards):
+        _check(self._l.nrf_set_shard(self._ctx, shard, n_shards))
+        self._shard = (shard, n_shards)
         self.W = self.H = 0
 
     def local_rays(self) -> int:
@@ -165,16 +168,10 @@ class NerfRender:
         _check(self._l.nrf_local_rays(self._ctx, C.byref(n)))
         return n.value
 
-    def shard_pixels(self):
-        """Global pixel index of every local ray (host arithmetic)."""
-        n = self.local_rays()
-        # vectorised restatement of shard_pixel(): blocks of `block` pixels round-robin (checked against
-        # nrf_shard_pixel in tests/test_host_logic.py)
-        q = np.arange(n, dtype=np.int64)
-        if n == self.W * self.H:
-            return q
-        b, s, ns = self._shard
-        return ((q // b) * ns + s) * b + q % b
+    def shard_pixel(self, q: int) -> int:
+        p = C.c_int()
+        _check(self._l.nrf_shard_pixel(self._ctx, q, C.byref(p)))
+        return p.value
 
     def device_outputs(self):
         a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()

@@ -1,88 +1,81 @@
 // kernels_composite.cu — front-to-back alpha compositing with early termination, finalisation and u8 packing.
 //
 // Replaces kernel_composite_rays (include/nerf-cuda/render_utils.h:658-751), get_image_and_depth (:241-265) and the
-// host-side u8 cast loop (src/nerf_render.cu:352-358).  One WARP per ray: lanes take 32 consecutive samples of the
-// ray's compact, ray-major sample range (coalesced 8 B + 4 B + 16 B loads), transmittance is an exclusive warp
-// product-scan of (1-alpha), the early-termination point is found with a ballot, and the weighted sums are warp
-// reductions.  The reference accumulates sequentially with T = 1 - sum(w); both are the same quantity in exact
-// arithmetic and differ by rounding only (image tolerance: max abs 2/255).
+// host-side u8 cast loop (src/nerf_render.cu:352-358).
+//
+// One THREAD per ray, one WARP per 8x4-pixel patch, the warp walking the patch's step-interleaved sample list in
+// lockstep: at step k the live lanes' samples are contiguous (k_emit's layout), so every load is one coalesced
+// segment, and the position of a lane's sample is a ballot + popc — the warp-cooperative part.  Each lane accumulates
+// its own ray sequentially in registers with exactly the reference's operations and order (T = 1 - sum(w), add the
+// sample, THEN stop if T < 1e-4, render_utils.h:717-727), so colour/depth differ from the oracle only through
+// __expf (ex2.approx) versus libm expf.
 #include "nrf_device.cuh"
 
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-
-extern "C" __global__ void __launch_bounds__(256)
-k_composite(int n_rays, const int* __restrict__ ray_offsets, const int* __restrict__ counts,
-            const float4* __restrict__ rays, const float* __restrict__ fars, const float4* __restrict__ samples,
+extern "C" __global__ void __launch_bounds__(128)
+k_composite(int n_rays, ShardMap map, const int* __restrict__ warp_base, const int* __restrict__ counts,
+            const float4* __restrict__ rays, const float2* __restrict__ far_tf, const float4* __restrict__ samples,
             const float* __restrict__ t_after, const uint2* __restrict__ sample_out, float* __restrict__ rgb_f32,
             float* __restrict__ depth_f32, int* __restrict__ used_counts, uint8_t* __restrict__ rgb_u8,
-            uint8_t* __restrict__ depth_u8) {
+            uint8_t* __restrict__ depth_u8, int u8_pixel_order) {
   const int lane = threadIdx.x & 31;
-  const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;   // n_rays is a multiple of 32: whole warps only
   if (q >= n_rays) return;
-  const int first = ray_offsets[q], cnt = counts[q];
-  float T = 1.0f;  // transmittance before the current chunk
+  const int cnt = counts[q];
+  const float4 ray = rays[q];
+  const float near = ray.w, far = far_tf[q].x;
+  int cmax = cnt;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, o));
+  const uint32_t lt = (1u << lane) - 1u;
+  long long off = warp_base[q >> 5];
   float wsum = 0.f, dep = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+  float tc = near, last_t = near;
   int used = 0;
-  for (int base = 0; base < cnt; base += 32) {
-    const int s = base + lane;
-    const bool valid = s < cnt;
-    float alpha = 0.f, ta = 0.f, r = 0.f, g = 0.f, b = 0.f;
-    if (valid) {
-      const uint2 o = __ldg(sample_out + first + s);
-      const float dt = __ldg(samples + first + s).w;
-      ta = __ldg(t_after + first + s);
+  bool running = true;
+  for (int k = 0; k < cmax; ++k) {
+    const bool has = k < cnt;
+    const uint32_t alive = __ballot_sync(0xffffffffu, has);
+    if (has && running) {
+      const long long i = off + __popc(alive & lt);
+      const uint2 o = __ldg(sample_out + i);
+      const float dt = __ldg(samples + i).w;
+      const float ta = __ldg(t_after + i);
       const __half2 rg = *reinterpret_cast<const __half2*>(&o.x);
       const __half2 bs = *reinterpret_cast<const __half2*>(&o.y);
-      r = __low2float(rg); g = __high2float(rg); b = __low2float(bs);
-      alpha = 1.0f - __expf(-__high2float(bs) * dt);
+      const float alpha = 1.0f - __expf(-__high2float(bs) * dt);
+      const float T = 1.0f - wsum;
+      const float w = alpha * T;
+      wsum += w;
+      tc += ta - last_t;   // deltas(1) = t - last_t (render_utils.h:629-631), accumulated like the reference
+      last_t = ta;
+      dep += w * tc;
+      cr += w * __low2float(rg);
+      cg += w * __high2float(rg);
+      cb += w * __low2float(bs);
+      ++used;
+      if ((double)T < 1e-4) running = false;   // the reference compares the float against a double literal
     }
-    // exclusive product scan of (1 - alpha) across the warp
-    float om = 1.0f - alpha, incl = om;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const float nb = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl *= nb;
-    }
-    float excl = __shfl_up_sync(0xffffffffu, incl, 1);
-    if (lane == 0) excl = 1.0f;
-    const float Tl = T * excl;  // transmittance before this lane's sample
-    // reference: add the sample, THEN stop if T < 1e-4 (render_utils.h:727): keep lanes up to the first such lane
-    const unsigned term = __ballot_sync(0xffffffffu, valid && Tl < 1e-4f);
-    const int last = term ? (__ffs(term) - 1) : 31;
-    const bool take = valid && lane <= last;
-    const float w = take ? alpha * Tl : 0.f;
-    wsum += warp_sum(w);
-    dep += warp_sum(w * ta);
-    cr += warp_sum(w * r);
-    cg += warp_sum(w * g);
-    cb += warp_sum(w * b);
-    used += __popc(__ballot_sync(0xffffffffu, take));
-    if (term) break;
-    T *= __shfl_sync(0xffffffffu, incl, 31);
+    off += __popc(alive);
+    if (!__any_sync(0xffffffffu, has && running)) break;
   }
-  if (lane == 0) {
-    const float4 ray = rays[q];
-    const float near = ray.w, far = fars[q];
-    const float bg = 1.0f;  // m_bg_color, nerf_render.h:74
-    const float R = cr + (1.0f - wsum) * bg, G = cg + (1.0f - wsum) * bg, B = cb + (1.0f - wsum) * bg;
-    // defect D3: missed rays (near == far == FLT_MAX) give 0/0 in the reference; defined as 0 here and in the oracle
-    const float D = (far == near) ? 0.0f : fmaxf(dep - near, 0.0f) / (far - near);
-    rgb_f32[q * 3 + 0] = R; rgb_f32[q * 3 + 1] = G; rgb_f32[q * 3 + 2] = B;
-    depth_f32[q] = D;
-    used_counts[q] = used;
-    // (unsigned char)(255.0 * v): double multiply + truncation (nerf_render.cu:355-358); clamped where that is UB (D4)
-    const float v4[4] = {R, G, B, D};
-    uint8_t u[4];
+  const float bg = 1.0f;  // m_bg_color, nerf_render.h:74
+  const float R = cr + (1.0f - wsum) * bg, G = cg + (1.0f - wsum) * bg, B = cb + (1.0f - wsum) * bg;
+  // defect D3: missed rays (near == far == FLT_MAX) give 0/0 in the reference; defined as 0 here and in the oracle
+  const float D = (far == near) ? 0.0f : fmaxf(dep - near, 0.0f) / (far - near);
+  rgb_f32[q * 3 + 0] = R; rgb_f32[q * 3 + 1] = G; rgb_f32[q * 3 + 2] = B;
+  depth_f32[q] = D;
+  used_counts[q] = used;
+  // (unsigned char)(255.0 * v): double multiply + truncation (nerf_render.cu:355-358); clamped where that is UB (D4)
+  int px, py;
+  if (!shard_pixel_xy(map, q, px, py)) return;
+  const long long dst = u8_pixel_order ? (long long)py * map.W + px : shard_packed_index(q);
+  const float v4[4] = {R, G, B, D};
+  uint8_t u[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const double x = 255.0 * (double)v4[k];
-      u[k] = !(x >= 0.0) ? 0 : (x >= 255.0 ? 255 : (uint8_t)(int)x);
-    }
-    rgb_u8[q * 3 + 0] = u[0]; rgb_u8[q * 3 + 1] = u[1]; rgb_u8[q * 3 + 2] = u[2];
-    depth_u8[q] = u[3];
+  for (int k = 0; k < 4; ++k) {
+    const double x = 255.0 * (double)v4[k];
+    u[k] = !(x >= 0.0) ? 0 : (x >= 255.0 ? 255 : (uint8_t)(int)x);
   }
+  rgb_u8[dst * 3 + 0] = u[0]; rgb_u8[dst * 3 + 1] = u[1]; rgb_u8[dst * 3 + 2] = u[2];
+  depth_u8[dst] = u[3];
 }

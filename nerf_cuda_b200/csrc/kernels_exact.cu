@@ -10,10 +10,12 @@
 //   linear_transformer x2 (include/nerf-cuda/common_device.cuh:31-36), concat_network_in_and_out (:280-306).
 // Design: one pass over whole rays instead of a host-driven <=8-step wavefront with a blocking D2H per iteration
 // (src/nerf_render.cu:269-338).  Pass 1 counts samples per ray and reduces per block; a one-block scan gives block
-// bases; pass 2 re-marches and writes a COMPACT, ray-major sample list (warp-shuffle scan inside the block).
+// bases; pass 2 re-marches (from the first sample on) and writes a COMPACT sample list, step-interleaved inside each
+// warp of 32 neighbouring rays (ballot/popc position arithmetic, see k_emit).
 #include "nrf_device.cuh"
 
 #define RAYS_BLOCK 128
+#define NRF_MAX_GRID 512  // largest density_grid_size (check_arch)
 
 __device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(hi, fmaxf(lo, x)); }
 
@@ -56,17 +58,24 @@ struct Step {
   int level;
 };
 
-__device__ __forceinline__ bool march_step(const MarchParams& P, const float d[3], const float rd[3], float& t,
-                                           Step& s) {
+// Two IEEE divisions of the reference are replaced by values that are bit-identical by construction:
+//   1/mip_bound           mip_bound = min(2^level, bound): an exact power of two (reciprocal = exponent flip) or `bound`
+//                         itself (P.rbound = 1.0f/bound computed once on the host, IEEE)
+//   (n + .5 + .5*sign)/(H-1)   the numerator is the exact integer n or n+1, so the quotient comes from a table
+//                         lut[m] = (float)m / (float)(H-1) filled by the host's IEEE division (H+1 entries, shared memory)
+__device__ __forceinline__ bool march_step(const MarchParams& P, const float* __restrict__ lut, const float d[3],
+                                           const float rd[3], float& t, Step& s) {
   const float x = clampf(P.o[0] + t * d[0], -P.bound, P.bound);
   const float y = clampf(P.o[1] + t * d[1], -P.bound, P.bound);
   const float z = clampf(P.o[2] + t * d[2], -P.bound, P.bound);
   // mip_from_pos: frexpf exponent of the max-norm, clamped to [0, C-1]  (exact, done on the bit pattern)
   const float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
-  int e = (int)((__float_as_uint(mx) >> 23) & 0xffu) - 126;
+  const int e = (int)((__float_as_uint(mx) >> 23) & 0xffu) - 126;
   const int level = max(0, min((int)P.C - 1, e));
-  const float mip_bound = fminf(__uint_as_float((uint32_t)(127 + level) << 23), P.bound);
-  const float mip_rbound = 1 / mip_bound;
+  const float pow2 = __uint_as_float((uint32_t)(127 + level) << 23);
+  const bool capped = pow2 > P.bound;
+  const float mip_bound = capped ? P.bound : pow2;
+  const float mip_rbound = capped ? P.rbound : __uint_as_float((uint32_t)(127 - level) << 23);
   const uint32_t H = P.H;
   // reference: (int)clamp(0.5 /*double*/ * (x*rb+1) * H, 0, H-1).  0.5*H is exact in float and the double product is
   // exact, so one float multiply by (0.5f*H) rounds identically (DESIGN.md numerics contract).
@@ -74,7 +83,7 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const float d[3
   const int nx = (int)clampf((x * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
   const int ny = (int)clampf((y * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
   const int nz = (int)clampf((z * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
-  const uint32_t cell = level * H * H * H + nx * H * H + ny * H + nz;
+  const uint32_t cell = ((level * H + nx) * H + ny) * H + nz;
   const bool occ = (__ldg(P.occupancy + (cell >> 5)) >> (cell & 31u)) & 1u;
   if (occ) {
     s.x = x; s.y = y; s.z = z;
@@ -85,15 +94,42 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const float d[3
     s.level = level;
     return true;
   }
-  const float tx = (((nx + 0.5f + 0.5f * copysignf(1.0f, d[0])) / hm1 * 2.0f - 1.0f) * mip_bound - x) * rd[0];
-  const float ty = (((ny + 0.5f + 0.5f * copysignf(1.0f, d[1])) / hm1 * 2.0f - 1.0f) * mip_bound - y) * rd[1];
-  const float tz = (((nz + 0.5f + 0.5f * copysignf(1.0f, d[2])) / hm1 * 2.0f - 1.0f) * mip_bound - z) * rd[2];
+  // n + 0.5f + 0.5f*copysignf(1, d) is the integer n+1 (sign bit clear, incl. +0) or n (sign bit set, incl. -0)
+  const float qx = lut[nx + 1 - (int)(__float_as_uint(d[0]) >> 31)];
+  const float qy = lut[ny + 1 - (int)(__float_as_uint(d[1]) >> 31)];
+  const float qz = lut[nz + 1 - (int)(__float_as_uint(d[2]) >> 31)];
+  const float tx = ((qx * 2.0f - 1.0f) * mip_bound - x) * rd[0];
+  const float ty = ((qy * 2.0f - 1.0f) * mip_bound - y) * rd[1];
+  const float tz = ((qz * 2.0f - 1.0f) * mip_bound - z) * rd[2];
   const float tt = t + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
   do {
     const float dt = clampf(t * P.dt_gamma, P.dt_min, P.dt_max);
     t += dt;
   } while (t < tt);
   return false;
+}
+
+__device__ __forceinline__ void load_lut(const MarchParams& P, float* lut) {
+  for (uint32_t i = threadIdx.x; i <= P.H; i += blockDim.x) lut[i] = __ldg(P.div_lut + i);
+  __syncthreads();
+}
+
+// Whole-ray count; t_first = the t at which the first sample was taken (pass 2 restarts there: the march state is t)
+__device__ __forceinline__ int count_ray(const MarchParams& P, const float* lut, const float d[3], float near, float far,
+                                         float& t_first) {
+  const float rd[3] = {1 / d[0], 1 / d[1], 1 / d[2]};
+  float t = near;
+  int c = 0;
+  t_first = near;
+  Step s;
+  while (t < far && c < NRF_MAX_STEPS_D) {
+    const float t0 = t;
+    if (march_step(P, lut, d, rd, t, s)) {
+      if (c == 0) t_first = t0;
+      ++c;
+    }
+  }
+  return c;
 }
 
 // block-wide sum / exclusive scan helpers (128 threads, warp shuffles)
@@ -105,28 +141,7 @@ __device__ __forceinline__ int warp_incl_scan(int v) {
   }
   return v;
 }
-
-// Pass 1: rays for this shard + sample counts + per-block totals.
-// rays: float4 {dx,dy,dz,near}; fars; counts; block_sums[gridDim.x]
-extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
-k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, float4* __restrict__ rays,
-             float* __restrict__ fars, int* __restrict__ counts, int* __restrict__ block_sums) {
-  const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
-  int c = 0;
-  if (q < n_local) {
-    const int p = shard_pixel(map, q);
-    float d[3], near, far;
-    ray_dir(P, p, d);
-    near_far(P, d, near, far);
-    rays[q] = make_float4(d[0], d[1], d[2], near);
-    fars[q] = far;
-    const float rd[3] = {1 / d[0], 1 / d[1], 1 / d[2]};
-    float t = near;
-    Step s;
-    while (t < far && c < NRF_MAX_STEPS_D)
-      if (march_step(P, d, rd, t, s)) ++c;
-    counts[q] = c;
-  }
+__device__ __forceinline__ void block_total(int c, int* __restrict__ block_sums) {
   __shared__ int wsum[RAYS_BLOCK / 32];
   const int incl = warp_incl_scan(c);
   if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = incl;
@@ -137,39 +152,65 @@ k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, f
     for (int w = 0; w < RAYS_BLOCK / 32; ++w) s += wsum[w];
     block_sums[blockIdx.x] = s;
   }
+}
+
+// Pass 1: rays of this shard (patch-major order, ShardMap) + sample counts + per-block totals.
+// rays: float4 {dx,dy,dz,near}; far_tf: float2 {far, t_first}; counts; block_sums[gridDim.x]
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
+k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, float4* __restrict__ rays,
+             float2* __restrict__ far_tf, int* __restrict__ counts, int* __restrict__ block_sums) {
+  __shared__ float lut[NRF_MAX_GRID + 1];
+  load_lut(P, lut);
+  const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
+  int c = 0;
+  if (q < n_local) {
+    const int p = shard_pixel(map, q);
+    float d[3] = {0.f, 0.f, 1.f}, near = 0.f, far = 0.f, tf = 0.f;
+    if (p >= 0) {
+      ray_dir(P, p, d);
+      near_far(P, d, near, far);
+      c = count_ray(P, lut, d, near, far, tf);
+    }
+    rays[q] = make_float4(d[0], d[1], d[2], near);
+    far_tf[q] = make_float2(far, tf);
+    counts[q] = c;
+  }
+  block_total(c, block_sums);
+}
+
+// Rays only, for pixels [pix0, pix0+n) in plain pixel order (stage probe nrf_probe_rays).
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
+k_rays_given_pixels(const __grid_constant__ MarchParams P, int pix0, int n, float4* __restrict__ rays,
+                    float* __restrict__ fars) {
+  const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
+  if (q >= n) return;
+  float d[3], near, far;
+  ray_dir(P, pix0 + q, d);
+  near_far(P, d, near, far);
+  rays[q] = make_float4(d[0], d[1], d[2], near);
+  fars[q] = far;
 }
 
 // Count-only variant for externally supplied rays (stage probe nrf_probe_march).
 extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
 k_count_given(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays,
-              const float* __restrict__ fars, int* __restrict__ counts, int* __restrict__ block_sums) {
+              float2* __restrict__ far_tf, int* __restrict__ counts, int* __restrict__ block_sums) {
+  __shared__ float lut[NRF_MAX_GRID + 1];
+  load_lut(P, lut);
   const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
   int c = 0;
   if (q < n) {
     const float4 r = rays[q];
     const float d[3] = {r.x, r.y, r.z};
-    const float rd[3] = {1 / d[0], 1 / d[1], 1 / d[2]};
-    const float far = fars[q];
-    float t = r.w;
-    Step s;
-    while (t < far && c < NRF_MAX_STEPS_D)
-      if (march_step(P, d, rd, t, s)) ++c;
+    float tf;
+    c = count_ray(P, lut, d, r.w, far_tf[q].x, tf);
+    far_tf[q].y = tf;
     counts[q] = c;
   }
-  __shared__ int wsum[RAYS_BLOCK / 32];
-  const int incl = warp_incl_scan(c);
-  if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = incl;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int s = 0;
-#pragma unroll
-    for (int w = 0; w < RAYS_BLOCK / 32; ++w) s += wsum[w];
-    block_sums[blockIdx.x] = s;
-  }
+  block_total(c, block_sums);
 }
 
-// One-block exclusive scan of the per-block totals (in place); total[0] = sum, total[1] = #rays with samples is
-// accumulated elsewhere.  n_blocks <= 1024*64.
+// One-block exclusive scan of the per-block totals (in place); total[0] = sum.  n_blocks <= 1024*64.
 extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict__ block_sums, int n_blocks,
                                                                  unsigned long long* __restrict__ total) {
   __shared__ int wsum[32];
@@ -198,46 +239,68 @@ extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict
   if (threadIdx.x == 0) total[0] = (unsigned long long)carry_s;
 }
 
-// Pass 2: re-march and emit the compact sample list.  ray_offsets[q] = first sample of ray q (exclusive scan).
+// Pass 2: re-march (from t_first) and emit the compact sample list in WARP-INTERLEAVED order: the samples of one warp
+// (32 neighbouring rays, an 8x4 pixel patch) are stored step-major — step k of every ray that has a k-th sample, in
+// lane order, then step k+1 ... — so 32 consecutive samples are spatial neighbours (one thin slab of the patch), which
+// is what makes the hash-grid gather cache-coherent.  Position of (lane r, step k):
+//     warp_base + sum_{r'} min(c_r', k) + #{r' < r : c_r' > k}
+// evaluated incrementally per lane from a per-warp table died[k] = {r' : c_r' == k+1} in shared memory, so lanes do not
+// march in lockstep.  warp_base[] (first sample of every warp) is kept for the composite kernel.
 // samples: float4 {u,v,w,dt} (position already normalised: x*pos_w+0.5, nerf_render.cu:311-312), t_after, ray id.
-// dbg (optional, probe only): per sample {x,y,z,dt,t_after,level,cell,ray} raw.
+// dbg (optional, probe only): per sample {x,y,z,dt,t_after,level,cell,ray} raw, RAY-major at dbg_offsets[q] + k.
 extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
-k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays, const float* __restrict__ fars,
-       const int* __restrict__ counts, const int* __restrict__ block_bases, int* __restrict__ ray_offsets,
+k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays, const float2* __restrict__ far_tf,
+       const int* __restrict__ counts, const int* __restrict__ block_bases, int* __restrict__ warp_base,
        float4* __restrict__ samples, float* __restrict__ t_after, int* __restrict__ sample_ray,
-       float* __restrict__ dbg, long long capacity) {
-  const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
-  const int c_total = (q < n) ? counts[q] : 0;
+       float* __restrict__ dbg, const long long* __restrict__ dbg_offsets, long long capacity) {
+  __shared__ float lut[NRF_MAX_GRID + 1];
   __shared__ int wsum[RAYS_BLOCK / 32];
+  __shared__ uint32_t died[RAYS_BLOCK / 32][NRF_MAX_STEPS_D];
+  load_lut(P, lut);
+  const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c_total = (q < n) ? counts[q] : 0;
   const int incl = warp_incl_scan(c_total);
-  if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = incl;
+  if (lane == 31) wsum[warp] = incl;
+  // per-warp table of the lanes that run out of samples after step k
+  int cmax = c_total;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, o));
+  for (int k = lane; k < cmax; k += 32) died[warp][k] = 0u;
+  __syncwarp();
+  if (c_total > 0) atomicOr(&died[warp][c_total - 1], 1u << lane);
   __syncthreads();
-  int base = block_bases[blockIdx.x];
-  for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) base += wsum[w];
-  const long long first = (long long)base + incl - c_total;
-  if (q >= n) return;
-  ray_offsets[q] = (int)first;
-  if (c_total == 0 || first + c_total > capacity) return;
+  long long base = block_bases[blockIdx.x];
+  for (int w = 0; w < warp; ++w) base += wsum[w];
+  if (lane == 0 && q < n) warp_base[q >> 5] = (int)base;
+  uint32_t alive = __ballot_sync(0xffffffffu, c_total > 0);
+  if (c_total == 0 || base + wsum[warp] > capacity) return;
+  const uint32_t lt = (1u << lane) - 1u;
   const float4 r = rays[q];
   const float d[3] = {r.x, r.y, r.z};
   const float rd[3] = {1 / d[0], 1 / d[1], 1 / d[2]};
-  const float far = fars[q];
-  float t = r.w;
+  const float2 ft = far_tf[q];
+  const float far = ft.x;
+  float t = ft.y;
   int c = 0;
+  long long off = base;
+  const long long dbg0 = dbg ? dbg_offsets[q] : 0;
   Step s;
   while (t < far && c < c_total) {
-    if (!march_step(P, d, rd, t, s)) continue;
-    const long long k = first + c;
+    if (!march_step(P, lut, d, rd, t, s)) continue;
+    const long long k = off + __popc(alive & lt);
     samples[k] = make_float4(P.pos_w * s.x + 0.5f, P.pos_w * s.y + 0.5f, P.pos_w * s.z + 0.5f, s.dt);
     t_after[k] = t;
     sample_ray[k] = q;
     if (dbg) {
-      float* o = dbg + k * 8;
+      float* o = dbg + (dbg0 + c) * 8;
       o[0] = s.x; o[1] = s.y; o[2] = s.z; o[3] = s.dt; o[4] = t;
       o[5] = __int_as_float(s.level);
       o[6] = __uint_as_float(s.cell);
       o[7] = __int_as_float(q);
     }
+    off += __popc(alive);
+    alive &= ~died[warp][c];
     ++c;
   }
 }

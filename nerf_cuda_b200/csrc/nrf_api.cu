@@ -28,19 +28,21 @@
 
 // kernels (kernels_exact.cu, kernels_network.cu, kernels_composite.cu)
 extern "C" {
-__global__ void k_rays_count(const MarchParams P, ShardMap map, int n_local, float4* rays, float* fars, int* counts,
+__global__ void k_rays_count(const MarchParams P, ShardMap map, int n_local, float4* rays, float2* far_tf, int* counts,
                              int* block_sums);
-__global__ void k_count_given(const MarchParams P, int n, const float4* rays, const float* fars, int* counts,
+__global__ void k_rays_given_pixels(const MarchParams P, int pix0, int n, float4* rays, float* fars);
+__global__ void k_count_given(const MarchParams P, int n, const float4* rays, float2* far_tf, int* counts,
                               int* block_sums);
 __global__ void k_scan_blocks(int* block_sums, int n_blocks, unsigned long long* total);
-__global__ void k_emit(const MarchParams P, int n, const float4* rays, const float* fars, const int* counts,
-                       const int* block_bases, int* ray_offsets, float4* samples, float* t_after, int* sample_ray,
-                       float* dbg, long long capacity);
+__global__ void k_emit(const MarchParams P, int n, const float4* rays, const float2* far_tf, const int* counts,
+                       const int* block_bases, int* warp_base, float4* samples, float* t_after, int* sample_ray,
+                       float* dbg, const long long* dbg_offsets, long long capacity);
 __global__ void k_build_occupancy(const float* grid, uint32_t n_cells, float thresh, uint32_t* bits);
 __global__ void k_cast_half(const float* in, __half* out, size_t n);
-__global__ void k_composite(int n_rays, const int* ray_offsets, const int* counts, const float4* rays,
-                            const float* fars, const float4* samples, const float* t_after, const uint2* sample_out,
-                            float* rgb_f32, float* depth_f32, int* used_counts, uint8_t* rgb_u8, uint8_t* depth_u8);
+__global__ void k_composite(int n_rays, ShardMap map, const int* warp_base, const int* counts, const float4* rays,
+                            const float2* far_tf, const float4* samples, const float* t_after, const uint2* sample_out,
+                            float* rgb_f32, float* depth_f32, int* used_counts, uint8_t* rgb_u8, uint8_t* depth_u8,
+                            int u8_pixel_order);
 size_t nrf_network_smem_bytes();
 cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t stream, const NetParams* P, int n,
                                const float4* samples, const int* sample_ray, const float4* rays, int dirs_mode,
@@ -116,7 +118,7 @@ static int check_arch(const nrf_model_desc& d) {
   if (d.rgb_activation > NRF_ACT_SIGMOID || d.sigma_activation > NRF_ACT_SIGMOID)
     return fail(NRF_EINVAL, "unsupported activation id");
   if (!(d.bound > 0) || d.cascades == 0 || d.cascades > 8 || d.grid_size == 0 || d.grid_size > 512 ||
-      (d.grid_size * d.grid_size * d.grid_size) % 32 != 0)
+      d.grid_size < 2 || (d.grid_size * d.grid_size * d.grid_size) % 32 != 0)
     return fail(NRF_EINVAL, "bad scene description (bound/cascades/grid_size)");
   return NRF_OK;
 }
@@ -180,18 +182,21 @@ struct Device {
   int dev = 0, n_sms = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[6] = {};
-  ShardMap map{0, 1, 1, 0};
+  cudaEvent_t done = nullptr;  // composite finished (cross-device wait before the frame copy)
+  ShardMap map{0, 1, 0, 0, 0, 0};
   int n_local = 0;
   // model replica
   DevBuf<__half> params_h;     // all params as fp16 (mlp row-major 10240 | table)
   DevBuf<uint4> mlp_packed;    // 1280 x 16 B
   DevBuf<uint32_t> occupancy;
+  DevBuf<float> div_lut;
   NetParams net{};
   MarchParams march{};
   // per-frame buffers
   DevBuf<float4> rays, samples;
-  DevBuf<float> fars, t_after, rgb_f32, depth_f32;
-  DevBuf<int> counts, ray_offsets, block_sums, sample_ray, used;
+  DevBuf<float2> far_tf;
+  DevBuf<float> t_after, rgb_f32, depth_f32;
+  DevBuf<int> counts, warp_base, block_sums, sample_ray, used;
   DevBuf<uint2> sample_out;
   DevBuf<uint8_t> rgb_u8, depth_u8;
   DevBuf<unsigned long long> total;
@@ -210,8 +215,8 @@ struct nrf_ctx {
   float aabb[6] = {};
   bool loaded = false;
   int W = 0, H = 0;
-  int shard = 0, n_shards = 1, block_pixels = 1024;  // process-level sharding (torchrun); devices subdivide further
-  uint8_t* rgb_host = nullptr;    // pinned, W*H*3 (full frame when n_shards == 1, else local rays packed)
+  int shard = 0, n_shards = 1;    // process-level sharding (one process per GPU); requires a single-device context
+  uint8_t* rgb_host = nullptr;    // pinned, W*H*3 (full frame when n_shards == 1, else this shard's packed tiles)
   uint8_t* depth_host = nullptr;  // pinned, W*H
   nrf_stats stats{};
   int net_grid_ctas_per_sm = 0;
@@ -236,6 +241,7 @@ extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
     cudaError_t e = cudaSetDevice(D.dev);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&D.stream, cudaStreamNonBlocking);
     for (int k = 0; k < 6 && e == cudaSuccess; ++k) e = cudaEventCreate(&D.ev[k]);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&D.done, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaMallocHost(&D.total_h, 4 * sizeof(unsigned long long));
     cudaDeviceProp prop;
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, D.dev);
@@ -255,13 +261,14 @@ extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
 
 static void free_device(Device& D) {
   cudaSetDevice(D.dev);
-  D.params_h.release(); D.mlp_packed.release(); D.occupancy.release();
-  D.rays.release(); D.samples.release(); D.fars.release(); D.t_after.release(); D.rgb_f32.release();
-  D.depth_f32.release(); D.counts.release(); D.ray_offsets.release(); D.block_sums.release();
+  D.params_h.release(); D.mlp_packed.release(); D.occupancy.release(); D.div_lut.release();
+  D.rays.release(); D.samples.release(); D.far_tf.release(); D.t_after.release(); D.rgb_f32.release();
+  D.depth_f32.release(); D.counts.release(); D.warp_base.release(); D.block_sums.release();
   D.sample_ray.release(); D.used.release(); D.sample_out.release(); D.rgb_u8.release(); D.depth_u8.release();
   D.total.release(); D.enc.release(); D.idx.release(); D.dbg.release();
   if (D.total_h) cudaFreeHost(D.total_h);
   for (int k = 0; k < 6; ++k) if (D.ev[k]) cudaEventDestroy(D.ev[k]);
+  if (D.done) cudaEventDestroy(D.done);
   if (D.stream) cudaStreamDestroy(D.stream);
 }
 
@@ -300,6 +307,11 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
   pack_weight(params + 3072, 64, 32, packed.data() + 3072);
   pack_weight(params + 5120, 64, 64, packed.data() + 5120);
   pack_weight(params + 9216, 16, 64, packed.data() + 9216);
+  // division table of the march: lut[m] = (float)m / (float)(H-1), IEEE division on the host (kernels_exact.cu)
+  std::vector<float> lut(d.grid_size + 1);
+  for (uint32_t m = 0; m <= d.grid_size; ++m) lut[m] = (float)m / (float)(d.grid_size - 1);
+  CU(D.div_lut.ensure(lut.size()));
+  CU(cudaMemcpyAsync(D.div_lut.p, lut.data(), lut.size() * sizeof(float), cudaMemcpyHostToDevice, D.stream));
   CU(D.mlp_packed.ensure(1280));
   CU(cudaMemcpyAsync(D.mlp_packed.p, packed.data(), 20480, cudaMemcpyHostToDevice, D.stream));
   CU(cudaStreamSynchronize(D.stream));
@@ -332,7 +344,9 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
   M.pos_w = 1.0 / (2 * d.bound);                  // nerf_render.cu:311-312
   M.C = d.cascades;
   M.H = d.grid_size;
+  M.rbound = 1.0f / d.bound;
   M.occupancy = D.occupancy.p;
+  M.div_lut = D.div_lut.p;
   return NRF_OK;
 }
 
@@ -417,12 +431,12 @@ extern "C" int nrf_get_model_desc(nrf_ctx* c, nrf_model_desc* out) {
 }
 
 // ---------------------------------------------------------------------------------------------------- resolution
-extern "C" int nrf_set_shard(nrf_ctx* c, int shard, int n_shards, int block_pixels) {
-  if (!c || n_shards < 1 || shard < 0 || shard >= n_shards || block_pixels < 1)
-    return fail(NRF_EINVAL, "nrf_set_shard: bad arguments");
+extern "C" int nrf_set_shard(nrf_ctx* c, int shard, int n_shards) {
+  if (!c || n_shards < 1 || shard < 0 || shard >= n_shards) return fail(NRF_EINVAL, "nrf_set_shard: bad arguments");
+  if (n_shards > 1 && c->devs.size() != 1)
+    return fail(NRF_EINVAL, "process-level sharding needs a single-device context (one process per GPU)");
   c->shard = shard;
   c->n_shards = n_shards;
-  c->block_pixels = block_pixels;
   c->W = c->H = 0;  // force re-allocation on the next set_resolution
   return NRF_OK;
 }
@@ -431,27 +445,45 @@ extern "C" int nrf_set_shard(nrf_ctx* c, int shard, int n_shards, int block_pixe
 extern "C" int nrf_set_resolution(nrf_ctx* c, int W, int H) {
   if (!c || W < 1 || H < 1) return fail(NRF_EINVAL, "nrf_set_resolution: bad arguments");
   if (!c->loaded) return fail(NRF_ESTATE, "set_resolution must follow reload_network_from_file");  // nerf_render.cu:226
-  if ((long long)W * H > (1ll << 30)) return fail(NRF_EINVAL, "resolution too large");
+  if ((long long)W * H > (1ll << 29)) return fail(NRF_EINVAL, "resolution too large");
   if (c->W == W && c->H == H) return NRF_OK;
   const int n_dev = (int)c->devs.size();
   const int total_shards = c->n_shards * n_dev;
+  // Several devices in one process write their pixels straight into device 0's frame over NVLink (peer stores)
+  for (int g = 1; g < n_dev; ++g) {
+    int can = 0;
+    CU(cudaDeviceCanAccessPeer(&can, c->devs[g].dev, c->devs[0].dev));
+    if (!can) return fail(NRF_ENODEV, "device %d cannot access device %d (peer access is required for n_gpus > 1)",
+                          c->devs[g].dev, c->devs[0].dev);
+    CU(cudaSetDevice(c->devs[g].dev));
+    cudaError_t e = cudaDeviceEnablePeerAccess(c->devs[0].dev, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CU(e);
+    cudaGetLastError();
+  }
   for (int g = 0; g < n_dev; ++g) {
     Device& D = c->devs[g];
     CU(cudaSetDevice(D.dev));
-    D.map = ShardMap{c->shard * n_dev + g, total_shards, total_shards == 1 ? 1 : c->block_pixels, W * H};
+    D.map = make_shard_map(c->shard * n_dev + g, total_shards, W, H);
     D.n_local = shard_local_count(D.map);
-    const size_t N = (size_t)std::max(D.n_local, 1);
+    const size_t N = (size_t)std::max(D.n_local, 32);
     const size_t nb = (N + 127) / 128;
-    CU(D.rays.ensure(N)); CU(D.fars.ensure(N)); CU(D.counts.ensure(N)); CU(D.ray_offsets.ensure(N));
+    CU(D.rays.ensure(N)); CU(D.far_tf.ensure(N)); CU(D.counts.ensure(N)); CU(D.warp_base.ensure((N + 31) / 32));
     CU(D.block_sums.ensure(nb)); CU(D.used.ensure(N)); CU(D.rgb_f32.ensure(N * 3)); CU(D.depth_f32.ensure(N));
-    CU(D.rgb_u8.ensure(N * 3)); CU(D.depth_u8.ensure(N)); CU(D.total.ensure(4));
+    CU(D.total.ensure(4));
+    // u8 outputs: whole-frame contexts keep ONE frame in pixel order on device 0; a sharded context keeps its packed tiles
+    if (g == 0) {
+      const size_t px = c->n_shards == 1 ? (size_t)W * H : N;
+      CU(D.rgb_u8.ensure(px * 3)); CU(D.depth_u8.ensure(px));
+      CU(cudaMemsetAsync(D.rgb_u8.p, 0, px * 3, D.stream)); CU(cudaMemsetAsync(D.depth_u8.p, 0, px, D.stream));
+    }
     D.march.W = W;
   }
   if (c->rgb_host) cudaFreeHost(c->rgb_host);
   if (c->depth_host) cudaFreeHost(c->depth_host);
   c->rgb_host = c->depth_host = nullptr;
-  CU(cudaMallocHost(&c->rgb_host, (size_t)W * H * 3));
-  CU(cudaMallocHost(&c->depth_host, (size_t)W * H));
+  const size_t host_px = c->n_shards == 1 ? (size_t)W * H : (size_t)std::max(c->devs[0].n_local, 1);
+  CU(cudaMallocHost(&c->rgb_host, host_px * 3));
+  CU(cudaMallocHost(&c->depth_host, host_px));
   c->W = W;
   c->H = H;
   return NRF_OK;
@@ -468,6 +500,7 @@ extern "C" int nrf_local_rays(nrf_ctx* c, int* n_local) {
 
 extern "C" int nrf_shard_pixel(nrf_ctx* c, int q, int* pixel) {
   if (!c || !pixel || !c->W) return fail(NRF_EINVAL, "bad argument / state");
+  if (q < 0 || q >= c->devs[0].n_local) return fail(NRF_EINVAL, "local ray index out of range");
   *pixel = shard_pixel(c->devs[0].map, q);
   return NRF_OK;
 }
@@ -529,7 +562,7 @@ static int frame_phase_a(nrf_ctx* c, Device& D, const float intr[4], const float
   const int nb = (D.n_local + 127) / 128;
   CU(cudaEventRecord(D.ev[0], D.stream));
   if (D.n_local > 0) {
-    k_rays_count<<<nb, 128, 0, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.fars.p, D.counts.p, D.block_sums.p);
+    k_rays_count<<<nb, 128, 0, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p);
     CU(cudaGetLastError());
   }
   k_scan_blocks<<<1, 1024, 0, D.stream>>>(D.block_sums.p, D.n_local > 0 ? nb : 0, D.total.p);
@@ -539,8 +572,8 @@ static int frame_phase_a(nrf_ctx* c, Device& D, const float intr[4], const float
   return NRF_OK;
 }
 
-// Phase B: emit + network + composite (+ optional D2H of the u8 frame).
-static int frame_phase_b(nrf_ctx* c, Device& D, bool to_host) {
+// Phase B: emit + network + composite; the u8 pixels land in device 0's frame (peer stores from the other devices).
+static int frame_phase_b(nrf_ctx* c, Device& D) {
   CU(cudaSetDevice(D.dev));
   CU(cudaStreamSynchronize(D.stream));
   const unsigned long long S = D.total_h[0];
@@ -553,8 +586,8 @@ static int frame_phase_b(nrf_ctx* c, Device& D, bool to_host) {
   }
   const int nb = (D.n_local + 127) / 128;
   if (D.n_local > 0) {
-    k_emit<<<nb, 128, 0, D.stream>>>(D.march, D.n_local, D.rays.p, D.fars.p, D.counts.p, D.block_sums.p,
-                                    D.ray_offsets.p, D.samples.p, D.t_after.p, D.sample_ray.p, nullptr,
+    k_emit<<<nb, 128, 0, D.stream>>>(D.march, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
+                                    D.warp_base.p, D.samples.p, D.t_after.p, D.sample_ray.p, nullptr, nullptr,
                                     (long long)D.samples.n);
     CU(cudaGetLastError());
   }
@@ -563,41 +596,28 @@ static int frame_phase_b(nrf_ctx* c, Device& D, bool to_host) {
                         0, nullptr, D.sample_out.p, nullptr));
   CU(cudaEventRecord(D.ev[3], D.stream));
   if (D.n_local > 0) {
-    const int blocks = (int)(((size_t)D.n_local * 32 + 255) / 256);
-    k_composite<<<blocks, 256, 0, D.stream>>>(D.n_local, D.ray_offsets.p, D.counts.p, D.rays.p, D.fars.p, D.samples.p,
-                                              D.t_after.p, D.sample_out.p, D.rgb_f32.p, D.depth_f32.p, D.used.p,
-                                              D.rgb_u8.p, D.depth_u8.p);
+    Device& D0 = c->devs[0];
+    k_composite<<<nb, 128, 0, D.stream>>>(D.n_local, D.map, D.warp_base.p, D.counts.p, D.rays.p, D.far_tf.p, D.samples.p,
+                                          D.t_after.p, D.sample_out.p, D.rgb_f32.p, D.depth_f32.p, D.used.p,
+                                          D0.rgb_u8.p, D0.depth_u8.p, c->n_shards == 1 ? 1 : 0);
     CU(cudaGetLastError());
   }
   CU(cudaEventRecord(D.ev[4], D.stream));
-  if (to_host && D.n_local > 0) {
-    // scatter this device's packed pixels into the full host frame: blocks of `block` pixels at stride n_shards*block
-    const ShardMap& m = D.map;
-    if (m.n_shards == 1 || c->n_shards > 1) {
-      // single shard, or process-level sharding (host buffer is packed in local order; the gather is NCCL's job)
-      size_t off = 0;
-      if (c->n_shards > 1) for (const Device& E : c->devs) { if (&E == &D) break; off += E.n_local; }
-      CU(cudaMemcpyAsync(c->rgb_host + off * 3, D.rgb_u8.p, (size_t)D.n_local * 3, cudaMemcpyDeviceToHost, D.stream));
-      CU(cudaMemcpyAsync(c->depth_host + off, D.depth_u8.p, (size_t)D.n_local, cudaMemcpyDeviceToHost, D.stream));
-    } else {
-      const int full = D.n_local / m.block, tail = D.n_local - full * m.block;
-      const size_t bs = (size_t)m.block;
-      if (full > 0) {
-        CU(cudaMemcpy2DAsync(c->rgb_host + (size_t)m.shard * bs * 3, (size_t)m.n_shards * bs * 3, D.rgb_u8.p, bs * 3,
-                             bs * 3, full, cudaMemcpyDeviceToHost, D.stream));
-        CU(cudaMemcpy2DAsync(c->depth_host + (size_t)m.shard * bs, (size_t)m.n_shards * bs, D.depth_u8.p, bs, bs, full,
-                             cudaMemcpyDeviceToHost, D.stream));
-      }
-      if (tail > 0) {
-        const size_t p0 = (size_t)shard_pixel(m, full * m.block);
-        CU(cudaMemcpyAsync(c->rgb_host + p0 * 3, D.rgb_u8.p + (size_t)full * bs * 3, (size_t)tail * 3,
-                           cudaMemcpyDeviceToHost, D.stream));
-        CU(cudaMemcpyAsync(c->depth_host + p0, D.depth_u8.p + (size_t)full * bs, (size_t)tail, cudaMemcpyDeviceToHost,
-                           D.stream));
-      }
-    }
+  CU(cudaEventRecord(D.done, D.stream));
+  return NRF_OK;
+}
+
+// Frame copy to the pinned host buffers (device 0, after every device's composite).
+static int frame_to_host(nrf_ctx* c) {
+  Device& D0 = c->devs[0];
+  CU(cudaSetDevice(D0.dev));
+  for (size_t g = 1; g < c->devs.size(); ++g) CU(cudaStreamWaitEvent(D0.stream, c->devs[g].done, 0));
+  const size_t px = c->n_shards == 1 ? (size_t)c->W * c->H : (size_t)D0.n_local;
+  if (px > 0) {
+    CU(cudaMemcpyAsync(c->rgb_host, D0.rgb_u8.p, px * 3, cudaMemcpyDeviceToHost, D0.stream));
+    CU(cudaMemcpyAsync(c->depth_host, D0.depth_u8.p, px, cudaMemcpyDeviceToHost, D0.stream));
   }
-  CU(cudaEventRecord(D.ev[5], D.stream));
+  CU(cudaEventRecord(D0.ev[5], D0.stream));
   return NRF_OK;
 }
 
@@ -606,7 +626,9 @@ static int render_common(nrf_ctx* c, const float intr[4], const float* pose, boo
   if (!c->loaded) return fail(NRF_ESTATE, "render_frame before reload_network_from_file");
   if (!c->W) return fail(NRF_ESTATE, "render_frame before set_resolution");
   for (Device& D : c->devs) { int rc = frame_phase_a(c, D, intr, pose); if (rc) return rc; }
-  for (Device& D : c->devs) { int rc = frame_phase_b(c, D, to_host); if (rc) return rc; }
+  for (Device& D : c->devs) { int rc = frame_phase_b(c, D); if (rc) return rc; }
+  if (to_host) { int rc = frame_to_host(c); if (rc) return rc; }
+  else { CU(cudaSetDevice(c->devs[0].dev)); CU(cudaEventRecord(c->devs[0].ev[5], c->devs[0].stream)); }
   if (sync) {
     for (Device& D : c->devs) { CU(cudaSetDevice(D.dev)); CU(cudaStreamSynchronize(D.stream)); }
   }
@@ -656,7 +678,10 @@ extern "C" int nrf_get_float_frame(nrf_ctx* c, float* rgb_f32, float* depth_f32,
       CU(cudaMemcpy(u.data(), D.used.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
     }
     for (int q = 0; q < n; ++q) {
-      const size_t p = whole ? (size_t)shard_pixel(D.map, q) : off + q;
+      // whole-frame context: global pixel order; sharded context: the packed tile order of the u8 outputs
+      const long long pp = whole ? (long long)shard_pixel(D.map, q) : (long long)off + shard_packed_index(q);
+      if (pp < 0) continue;  // ray of an edge tile outside the image
+      const size_t p = (size_t)pp;
       if (rgb_f32) std::memcpy(rgb_f32 + p * 3, &r[(size_t)q * 3], 12);
       if (depth_f32) depth_f32[p] = d[q];
       if (samples_per_ray) samples_per_ray[p] = u[q];
@@ -708,27 +733,19 @@ extern "C" int nrf_probe_rays(nrf_ctx* c, const float intr[4], const float pose[
   M.W = W;
   for (int k = 0; k < 3; ++k) rays_o[k] = M.o[k];
   if (n == 0) return NRF_OK;
-  DevBuf<float4> r; DevBuf<float> f; DevBuf<int> cnt, bs;
-  const int nb = (n + 127) / 128;
-  CU(r.ensure(n)); CU(f.ensure(n)); CU(cnt.ensure(n)); CU(bs.ensure(nb));
-  // a shard map that starts at pix0: one shard, identity, offset applied by rendering [0, pix0+n) lazily is wasteful;
-  // instead use block == n, n_shards large enough that shard index selects the window when pix0 % n == 0, else fall
-  // back to rendering from 0.
-  ShardMap map{0, 1, 1, pix0 + n};
-  DevBuf<float4> rall; DevBuf<float> fall; DevBuf<int> call;
-  const int ntot = pix0 + n, nbt = (ntot + 127) / 128;
-  CU(rall.ensure(ntot)); CU(fall.ensure(ntot)); CU(call.ensure(ntot)); CU(bs.ensure(nbt));
-  k_rays_count<<<nbt, 128, 0, D.stream>>>(M, map, ntot, rall.p, fall.p, call.p, bs.p);
+  DevBuf<float4> r; DevBuf<float> f;
+  CU(r.ensure(n)); CU(f.ensure(n));
+  k_rays_given_pixels<<<(n + 127) / 128, 128, 0, D.stream>>>(M, pix0, n, r.p, f.p);
   CU(cudaGetLastError());
   std::vector<float4> hr(n);
-  CU(cudaMemcpyAsync(hr.data(), rall.p + pix0, (size_t)n * 16, cudaMemcpyDeviceToHost, D.stream));
-  CU(cudaMemcpyAsync(fars, fall.p + pix0, (size_t)n * 4, cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaMemcpyAsync(hr.data(), r.p, (size_t)n * 16, cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaMemcpyAsync(fars, f.p, (size_t)n * 4, cudaMemcpyDeviceToHost, D.stream));
   CU(cudaStreamSynchronize(D.stream));
   for (int i = 0; i < n; ++i) {
     rays_d[i * 3 + 0] = hr[i].x; rays_d[i * 3 + 1] = hr[i].y; rays_d[i * 3 + 2] = hr[i].z;
     nears[i] = hr[i].w;
   }
-  r.release(); f.release(); cnt.release(); bs.release(); rall.release(); fall.release(); call.release();
+  r.release(); f.release();
   return NRF_OK;
 }
 
@@ -741,12 +758,17 @@ extern "C" int nrf_probe_march(nrf_ctx* c, int n, const float rays_o[3], const f
   MarchParams M = D.march;
   for (int k = 0; k < 3; ++k) M.o[k] = rays_o[k];
   std::vector<float4> hr(n);
-  for (int i = 0; i < n; ++i) hr[i] = make_float4(rays_d[i * 3], rays_d[i * 3 + 1], rays_d[i * 3 + 2], nears[i]);
-  DevBuf<float4> r, smp; DevBuf<float> f, ta, dbg; DevBuf<int> cnt, bs, offs, sray; DevBuf<unsigned long long> tot;
+  std::vector<float2> hf(n);
+  for (int i = 0; i < n; ++i) {
+    hr[i] = make_float4(rays_d[i * 3], rays_d[i * 3 + 1], rays_d[i * 3 + 2], nears[i]);
+    hf[i] = make_float2(fars[i], nears[i]);
+  }
+  DevBuf<float4> r, smp; DevBuf<float2> f; DevBuf<float> ta, dbg; DevBuf<int> cnt, bs, wb, sray;
+  DevBuf<unsigned long long> tot; DevBuf<long long> doff;
   const int nb = (n + 127) / 128;
-  CU(r.ensure(n)); CU(f.ensure(n)); CU(cnt.ensure(n)); CU(bs.ensure(nb)); CU(offs.ensure(n)); CU(tot.ensure(4));
+  CU(r.ensure(n)); CU(f.ensure(n)); CU(cnt.ensure(n)); CU(bs.ensure(nb)); CU(wb.ensure((n + 31) / 32)); CU(tot.ensure(4));
   CU(cudaMemcpyAsync(r.p, hr.data(), (size_t)n * 16, cudaMemcpyHostToDevice, D.stream));
-  CU(cudaMemcpyAsync(f.p, fars, (size_t)n * 4, cudaMemcpyHostToDevice, D.stream));
+  CU(cudaMemcpyAsync(f.p, hf.data(), (size_t)n * 8, cudaMemcpyHostToDevice, D.stream));
   k_count_given<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p);
   CU(cudaGetLastError());
   k_scan_blocks<<<1, 1024, 0, D.stream>>>(bs.p, nb, tot.p);
@@ -759,15 +781,21 @@ extern "C" int nrf_probe_march(nrf_ctx* c, int n, const float rays_o[3], const f
   if (samples) {
     if (S > max_samples) rc = fail(NRF_EINVAL, "sample buffer too small: need %llu", S);
     else if (S > 0) {
+      // the probe returns the samples RAY-major (like the oracle); the frame path's interleaved list is also written
+      std::vector<long long> ho(n);
+      long long acc = 0;
+      for (int i = 0; i < n; ++i) { ho[i] = acc; acc += counts[i]; }
+      CU(doff.ensure(n));
+      CU(cudaMemcpyAsync(doff.p, ho.data(), (size_t)n * 8, cudaMemcpyHostToDevice, D.stream));
       CU(smp.ensure(S)); CU(ta.ensure(S)); CU(sray.ensure(S)); CU(dbg.ensure(S * 8));
-      k_emit<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p, offs.p, smp.p, ta.p, sray.p, dbg.p, (long long)S);
+      k_emit<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p, wb.p, smp.p, ta.p, sray.p, dbg.p, doff.p, (long long)S);
       CU(cudaGetLastError());
       CU(cudaMemcpyAsync(samples, dbg.p, (size_t)S * 32, cudaMemcpyDeviceToHost, D.stream));
       CU(cudaStreamSynchronize(D.stream));
     }
   }
-  r.release(); smp.release(); f.release(); ta.release(); dbg.release(); cnt.release(); bs.release(); offs.release();
-  sray.release(); tot.release();
+  r.release(); smp.release(); f.release(); ta.release(); dbg.release(); cnt.release(); bs.release(); wb.release();
+  sray.release(); tot.release(); doff.release();
   return rc;
 }
 

@@ -7,8 +7,10 @@
 //   mlp_rowmaj : __half[10240]            same weights, reference order [out][in] (SIMT check kernel only)
 //   occupancy  : uint32[C*H^3/32]         bit == (density > min(0.01, mean_density)), same linear cell index as
 //                                         the reference's float grid (render_utils.h:613-619)
-//   rays       : float4[N] {dx,dy,dz,near} + float[N] far
-//   samples    : float4[S] {u,v,w (position normalised to [0,1]), dt} + float[S] t_after + int[S] ray
+//   rays       : float4[N] {dx,dy,dz,near} + float2[N] {far, t_first}; N = local rays in patch-major order (ShardMap)
+//   samples    : float4[S] {u,v,w (position normalised to [0,1]), dt} + float[S] t_after + int[S] ray, in
+//                WARP-INTERLEAVED order: for each 32-ray patch, step k of all its live rays, then step k+1, ...
+//   warp_base  : int[N/32] first sample of each patch
 //   sample_out : uint2[S]  four halves {r,g,b,sigma}
 #pragma once
 #include <cuda_fp16.h>
@@ -45,7 +47,9 @@ struct MarchParams {
   float bound, dt_gamma, dt_min, dt_max, min_near, pos_w;
   uint32_t C, H;
   int W;            // image width
+  float rbound;     // 1/bound (IEEE, host)
   const uint32_t* occupancy;
+  const float* div_lut;  // div_lut[m] = (float)m / (float)(H-1), m = 0..H  (IEEE division done once on the host)
 };
 
 // activation ids mirror include/nerf_b200.h
@@ -54,26 +58,44 @@ struct MarchParams {
 #define ACT_EXP 2
 #define ACT_SIGMOID 3
 
-// Maps local ray index q of this shard to the global pixel index.  Shards interleave blocks of `block` pixels
-// round-robin (balance + locality); n_shards == 1 => identity.
+// Ray order and sharding.  The image is cut into 32x32-pixel tiles; tile t belongs to shard t % n_shards (round-robin
+// for balance; the reference interleaves single pixels, pixel = NGPU*tid + gpu, render_utils.h:37).
+// Inside a tile rays are ordered patch-major: 32 patches of 8x4 pixels, 32 rays (one WARP) per patch, so that the 32
+// lanes of every march / composite warp — and, through the step-interleaved sample list, of every gather warp — are
+// spatial neighbours.  Local ray index q = local_tile*1024 + patch*32 + lane.  Tiles that stick out of
+// the image contain invalid rays (pixel -1, zero samples).
+#define NRF_TILE_PX 32
 struct ShardMap {
-  int shard, n_shards, block, n_pixels;
+  int shard, n_shards, W, H, tiles_x, tiles_y;
 };
-__host__ __device__ inline int shard_local_count(const ShardMap& m) {
-  if (m.n_shards == 1) return m.n_pixels;
-  const int n_blocks = (m.n_pixels + m.block - 1) / m.block;
-  int cnt = 0;
-  // blocks b with b % n_shards == shard
-  const int full = n_blocks / m.n_shards, rem = n_blocks % m.n_shards;
-  const int mine = full + (m.shard < rem ? 1 : 0);
-  cnt = mine * m.block;
-  // the last block overall may be partial
-  const int last = n_blocks - 1;
-  if (last >= 0 && last % m.n_shards == m.shard) cnt -= n_blocks * m.block - m.n_pixels;
-  return cnt;
+__host__ __device__ inline ShardMap make_shard_map(int shard, int n_shards, int W, int H) {
+  ShardMap m;
+  m.shard = shard; m.n_shards = n_shards; m.W = W; m.H = H;
+  m.tiles_x = (W + NRF_TILE_PX - 1) / NRF_TILE_PX;
+  m.tiles_y = (H + NRF_TILE_PX - 1) / NRF_TILE_PX;
+  return m;
+}
+__host__ __device__ inline int shard_tile_count(const ShardMap& m) {
+  const int n = m.tiles_x * m.tiles_y;
+  return n / m.n_shards + (m.shard < n % m.n_shards ? 1 : 0);
+}
+__host__ __device__ inline int shard_local_count(const ShardMap& m) { return shard_tile_count(m) * (NRF_TILE_PX * NRF_TILE_PX); }
+// local ray q -> pixel coordinates; returns false for rays outside the image
+__host__ __device__ inline bool shard_pixel_xy(const ShardMap& m, int q, int& px, int& py) {
+  const int lt = q >> 10, w = q & 1023, patch = w >> 5, lane = w & 31;
+  const int tile = lt * m.n_shards + m.shard;
+  const int tx = tile % m.tiles_x, ty = tile / m.tiles_x;
+  px = tx * NRF_TILE_PX + (patch & 3) * 8 + (lane & 7);
+  py = ty * NRF_TILE_PX + (patch >> 2) * 4 + (lane >> 3);
+  return px < m.W && py < m.H;
 }
 __host__ __device__ inline int shard_pixel(const ShardMap& m, int q) {
-  if (m.n_shards == 1) return q;
-  const int lb = q / m.block, off = q - lb * m.block;
-  return (lb * m.n_shards + m.shard) * m.block + off;
+  int px, py;
+  return shard_pixel_xy(m, q, px, py) ? py * m.W + px : -1;
+}
+// Position of local ray q in the PACKED u8 output of a sharded context: tiles in local order, pixels row-major inside
+// the 32x32 tile (what multigpu.FrameSharding.assemble un-tiles after the gather).
+__host__ __device__ inline int shard_packed_index(int q) {
+  const int lt = q >> 10, w = q & 1023, patch = w >> 5, lane = w & 31;
+  return lt * 1024 + ((patch >> 2) * 4 + (lane >> 3)) * NRF_TILE_PX + (patch & 3) * 8 + (lane & 7);
 }

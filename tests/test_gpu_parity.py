@@ -183,3 +183,35 @@ def test_set_resolution_idempotent_and_resize(pair):
     r.set_resolution((32, 32))
     b, _ = r.render_frame(intr, pose)
     assert np.array_equal(a, b)   # idempotent + deterministic
+
+
+def test_sharded_contexts_assemble_to_the_same_frame(pair):
+    """One-process-per-GPU path on a single GPU: every shard renders its 32x32 tiles, the packed u8 tiles assemble
+    (multigpu.FrameSharding) to exactly the frame of the unsharded context; float outputs agree slot by slot."""
+    import torch
+    from nerf_cuda_b200.multigpu import FrameSharding
+    name, sc, r, O = pair
+    W, H, world = 100, 70, 3
+    intr, pose = syn.intrinsics(W, H), syn.look_at_pose(syn.camera_radius(name), 20.0, 100.0)
+    r.set_shard(0, 1)
+    r.set_resolution((W, H))
+    full_u8 = r.render_frame(intr, pose)[0].copy()
+    full_f, _, full_cnt = r.float_frame()
+    sh = FrameSharding(W, H, world)
+    g = torch.zeros(world, sh.tiles_per_shard, 32, 32, 3, dtype=torch.uint8)
+    for s in range(world):
+        rs = NerfRender(1)
+        rs.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+        rs.set_shard(s, world)
+        rs.set_resolution((W, H))
+        assert rs.local_rays() == sh.local_count(s)
+        rgb, dep = rs.render_frame(intr, pose)
+        g[s, : rgb.shape[0]] = torch.from_numpy(rgb.copy())
+        f, _, cnt = rs.float_frame()
+        pk = sh.packed_pixels(s).reshape(-1)
+        assert np.array_equal(f[pk >= 0], full_f[pk[pk >= 0]]) and np.array_equal(cnt[pk >= 0], full_cnt[pk[pk >= 0]])
+        for q in (0, 31, 32, 1023, sh.local_count(s) - 1):
+            pq = rs.shard_pixel(q)
+            assert pq == -1 or 0 <= pq < W * H
+        rs.close()
+    assert np.array_equal(sh.assemble(g).numpy(), full_u8)

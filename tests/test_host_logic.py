@@ -86,31 +86,42 @@ def test_bad_descriptions_are_rejected(built_lib):
         capi.param_count(d)
 
 
-def _shard_pixels(n_pixels, shard, n_shards, block):
-    q = 0
-    out = []
-    for b in range((n_pixels + block - 1) // block):
-        if b % n_shards == shard:
-            out += list(range(b * block, min((b + 1) * block, n_pixels)))
-    return out
+def _ray_pixel(W, H, shard, n_shards, q):
+    """Independent restatement of ShardMap (csrc/nrf_device.cuh): q = local_tile*1024 + patch*32 + lane; tiles of 32x32
+    pixels round-robin over shards; 4x8 patches of 8x4 pixels per tile; lane = 8*row + col inside the patch."""
+    tiles_x = -(-W // 32)
+    lt, w = divmod(q, 1024)
+    patch, lane = divmod(w, 32)
+    tile = lt * n_shards + shard
+    ty, tx = divmod(tile, tiles_x)
+    px = tx * 32 + (patch % 4) * 8 + lane % 8
+    py = ty * 32 + (patch // 4) * 4 + lane // 8
+    return py * W + px if px < W and py < H else -1
 
 
-@pytest.mark.parametrize("n_pixels,n_shards,block", [(1000, 3, 128), (1920 * 4, 8, 128), (77, 2, 1), (5, 8, 4), (4096, 4, 1024)])
-def test_shard_map_partitions_the_frame(n_pixels, n_shards, block):
-    """Python restatement of ShardMap (csrc/nrf_device.cuh) used by NerfRender.shard_pixels: shards are disjoint and
-    cover every pixel exactly once; block_pixels = 1 reproduces the reference's interleave pixel = NGPU*tid + gpu
-    (render_utils.h:37)."""
-    seen = np.zeros(n_pixels, np.int32)
-    for s in range(n_shards):
-        want = np.array(_shard_pixels(n_pixels, s, n_shards, block), np.int64)
-        q = np.arange(want.size, dtype=np.int64)
-        got = ((q // block) * n_shards + s) * block + q % block
-        assert np.array_equal(got, want)
-        seen[want] += 1
+@pytest.mark.parametrize("W,H,world", [(100, 80, 1), (100, 80, 3), (1920, 1080, 8), (33, 17, 2), (64, 64, 4), (31, 5, 8)])
+def test_tile_sharding_partitions_the_frame(W, H, world):
+    """FrameSharding (host side of the N>1 path) against the ray order the kernels use: shards are disjoint, cover every
+    pixel exactly once, and a 32-lane warp is one 8x4-pixel patch."""
+    from nerf_cuda_b200.multigpu import FrameSharding
+    sh = FrameSharding(W, H, world)
+    seen = np.zeros(W * H, np.int32)
+    for s in range(world):
+        pk = sh.packed_pixels(s)
+        assert pk.shape == (sh.local_tiles(s), 32, 32) and sh.local_count(s) == pk.size
+        valid = pk[pk >= 0]
+        seen[valid] += 1
+        # ray order -> pixel, checked on a sample of slots (all of them for small frames)
+        n = sh.local_count(s)
+        qs = np.arange(n) if n <= 8192 else np.random.default_rng(s).integers(0, n, 4096)
+        for q in qs:
+            p = _ray_pixel(W, H, s, world, int(q))
+            lt, w = divmod(int(q), 1024)
+            patch, lane = divmod(w, 32)
+            yin, xin = (patch // 4) * 4 + lane // 8, (patch % 4) * 8 + lane % 8
+            assert pk[lt, yin, xin] == p
     assert (seen == 1).all()
-    if block == 1:
-        for s in range(n_shards):
-            assert _shard_pixels(n_pixels, s, n_shards, 1) == list(range(s, n_pixels, n_shards))
+    assert sum(sh.local_tiles(s) for s in range(world)) == sh.n_tiles
 
 
 def _inspect(path):

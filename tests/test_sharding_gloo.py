@@ -27,21 +27,20 @@ def _free_port():
     return p
 
 
-def _render_pixels(O, intr, pose, W, H, pixels, block):
-    """Oracle render of an arbitrary block-structured pixel list (contiguous runs of <= block pixels)."""
-    out = np.zeros((pixels.size, 3), np.float32)
-    i = 0
-    while i < pixels.size:
-        j = i
-        while j + 1 < pixels.size and pixels[j + 1] == pixels[j] + 1:
-            j += 1
-        rgb, _, _ = O.render(intr, pose, W, H, int(pixels[i]), j - i + 1)
-        out[i:j + 1] = rgb
-        i = j + 1
+def _render_packed(O, intr, pose, W, H, packed):
+    """Oracle render of a shard's packed tile slots ([tiles,32,32] global pixel or -1), row by row inside each tile."""
+    out = np.zeros(packed.shape + (3,), np.float32)
+    for t in range(packed.shape[0]):
+        for y in range(32):
+            row = packed[t, y]
+            n = int((row >= 0).sum())     # valid pixels of a tile row are a prefix (x grows along the row)
+            if n:
+                rgb, _, _ = O.render(intr, pose, W, H, int(row[0]), n)
+                out[t, y, :n] = rgb
     return out
 
 
-def _worker(rank, world, port, W, H, block, q):
+def _worker(rank, world, port, W, H, q):
     from oracle import orc
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -49,9 +48,8 @@ def _worker(rank, world, port, W, H, block, q):
         sc = syn.make_scene("tiny")
         O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
         intr, pose = syn.intrinsics(W, H), syn.look_at_pose(4.0, 20.0, 40.0)
-        sh = FrameSharding(W, H, world, block)
-        pix = sh.local_pixels(rank)
-        local = O.to_u8(_render_pixels(O, intr, pose, W, H, pix, block))
+        sh = FrameSharding(W, H, world)
+        local = O.to_u8(_render_packed(O, intr, pose, W, H, sh.packed_pixels(rank)))
         frame = FrameGather(sh, rank, "cpu")(torch.from_numpy(local))
         if rank == 0:
             full, _, _ = O.render(intr, pose, W, H)
@@ -63,14 +61,14 @@ def _worker(rank, world, port, W, H, block, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,W,H,block", [(2, 40, 24, 128), (2, 33, 17, 1), (3, 40, 24, 64)])
-def test_sharded_frame_equals_single_shard(world, W, H, block):
+@pytest.mark.parametrize("world,W,H", [(2, 72, 40), (2, 33, 17), (3, 100, 64)])
+def test_sharded_frame_equals_single_shard(world, W, H):
     from oracle import orc
     orc.lib()   # build once before forking
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, W, H, block, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, W, H, q)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
@@ -79,18 +77,11 @@ def test_sharded_frame_equals_single_shard(world, W, H, block):
     assert q.get(timeout=5) is True
 
 
-def test_sharding_counts_match_c_abi_rule():
-    for n_pix, world, block in [(1000, 3, 128), (1920 * 1080, 8, 128), (5, 8, 4), (64, 2, 1)]:
-        sh = FrameSharding(n_pix, 1, world, block)
-        tot = 0
+def test_assemble_inverts_the_packing():
+    for W, H, world in [(100, 70, 3), (1920, 1080, 8), (5, 8, 4), (64, 32, 2)]:
+        sh = FrameSharding(W, H, world)
+        g = torch.full((world, sh.tiles_per_shard, 32, 32, 1), -7, dtype=torch.int64)
         for r in range(world):
-            px = sh.local_pixels(r)
-            assert px.size == sh.local_count(r) <= sh.n_max
-            tot += px.size
-        assert tot == n_pix
-        # assemble() inverts the packing
-        g = torch.zeros(world, sh.n_max, 1, dtype=torch.int64)
-        for r in range(world):
-            px = sh.local_pixels(r)
-            g[r, : px.size, 0] = torch.from_numpy(px)
-        assert torch.equal(sh.assemble(g).reshape(-1), torch.arange(n_pix))
+            pk = sh.packed_pixels(r)
+            g[r, : pk.shape[0], :, :, 0] = torch.from_numpy(pk)
+        assert torch.equal(sh.assemble(g).reshape(-1), torch.arange(W * H))
