@@ -158,7 +158,8 @@ __device__ __forceinline__ void block_total(int c, int* __restrict__ block_sums)
 // rays: float4 {dx,dy,dz,near}; far_tf: float2 {far, t_first}; counts; block_sums[gridDim.x]
 extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
 k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, float4* __restrict__ rays,
-             float2* __restrict__ far_tf, int* __restrict__ counts, int* __restrict__ block_sums) {
+             float2* __restrict__ far_tf, int* __restrict__ counts, int* __restrict__ block_sums,
+             uint4* __restrict__ ray_sh) {
   __shared__ float lut[NRF_MAX_GRID + 1];
   load_lut(P, lut);
   const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
@@ -174,6 +175,12 @@ k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, f
     rays[q] = make_float4(d[0], d[1], d[2], near);
     far_tf[q] = make_float2(far, tf);
     counts[q] = c;
+    if (c > 0) {  // SH of the normalised direction d*0.5+0.5 (nerf_render.cu:313-314), once per ray
+      uint32_t sh[8];
+      sh4(0.5f * d[0] + 0.5f, 0.5f * d[1] + 0.5f, 0.5f * d[2] + 0.5f, sh);
+      ray_sh[2 * (size_t)q] = make_uint4(sh[0], sh[1], sh[2], sh[3]);
+      ray_sh[2 * (size_t)q + 1] = make_uint4(sh[4], sh[5], sh[6], sh[7]);
+    }
   }
   block_total(c, block_sums);
 }

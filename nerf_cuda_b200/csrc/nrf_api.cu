@@ -29,7 +29,7 @@
 // kernels (kernels_exact.cu, kernels_network.cu, kernels_composite.cu)
 extern "C" {
 __global__ void k_rays_count(const MarchParams P, ShardMap map, int n_local, float4* rays, float2* far_tf, int* counts,
-                             int* block_sums);
+                             int* block_sums, uint4* ray_sh);
 __global__ void k_rays_given_pixels(const MarchParams P, int pix0, int n, float4* rays, float* fars);
 __global__ void k_count_given(const MarchParams P, int n, const float4* rays, float2* far_tf, int* counts,
                               int* block_sums);
@@ -45,11 +45,10 @@ __global__ void k_composite(int n_rays, ShardMap map, const int* warp_base, cons
                             int u8_pixel_order);
 size_t nrf_network_smem_bytes();
 cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t stream, const NetParams* P, int n,
-                               const float4* samples, const int* sample_ray, const float4* rays, int dirs_mode,
-                               uint4* enc_io, uint2* out, uint32_t* idx_out);
+                               const float4* samples, const int* sample_ray, const float4* rays, const uint4* ray_sh,
+                               int dirs_mode, uint4* enc_io, uint2* out, uint32_t* idx_out);
 cudaError_t nrf_launch_network_simt(cudaStream_t stream, const NetParams* P, int n, const uint4* enc,
                                     const float4* dirs01, uint2* out);
-int nrf_network_occupancy(int mode);
 }
 
 // ---------------------------------------------------------------------------------------------------- errors
@@ -194,6 +193,7 @@ struct Device {
   MarchParams march{};
   // per-frame buffers
   DevBuf<float4> rays, samples;
+  DevBuf<uint4> ray_sh;
   DevBuf<float2> far_tf;
   DevBuf<float> t_after, rgb_f32, depth_f32;
   DevBuf<int> counts, warp_base, block_sums, sample_ray, used;
@@ -219,7 +219,6 @@ struct nrf_ctx {
   uint8_t* rgb_host = nullptr;    // pinned, W*H*3 (full frame when n_shards == 1, else this shard's packed tiles)
   uint8_t* depth_host = nullptr;  // pinned, W*H
   nrf_stats stats{};
-  int net_grid_ctas_per_sm = 0;
 };
 
 static int device_count() {
@@ -262,7 +261,7 @@ extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
 static void free_device(Device& D) {
   cudaSetDevice(D.dev);
   D.params_h.release(); D.mlp_packed.release(); D.occupancy.release(); D.div_lut.release();
-  D.rays.release(); D.samples.release(); D.far_tf.release(); D.t_after.release(); D.rgb_f32.release();
+  D.rays.release(); D.ray_sh.release(); D.samples.release(); D.far_tf.release(); D.t_after.release(); D.rgb_f32.release();
   D.depth_f32.release(); D.counts.release(); D.warp_base.release(); D.block_sums.release();
   D.sample_ray.release(); D.used.release(); D.sample_out.release(); D.rgb_u8.release(); D.depth_u8.release();
   D.total.release(); D.enc.release(); D.idx.release(); D.dbg.release();
@@ -331,6 +330,7 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
   }
   N.mlp_rowmaj = D.params_h.p;
   N.table = reinterpret_cast<const __half2*>(D.params_h.p + 10240);
+  for (uint32_t l = 0; l < d.n_levels; ++l) N.lv[l].tab = reinterpret_cast<const uint32_t*>(N.table) + N.lv[l].offset;
   N.mlp_packed = D.mlp_packed.p;
   N.rgb_act = d.rgb_activation;
   N.sigma_act = d.sigma_activation;
@@ -467,7 +467,7 @@ extern "C" int nrf_set_resolution(nrf_ctx* c, int W, int H) {
     D.n_local = shard_local_count(D.map);
     const size_t N = (size_t)std::max(D.n_local, 32);
     const size_t nb = (N + 127) / 128;
-    CU(D.rays.ensure(N)); CU(D.far_tf.ensure(N)); CU(D.counts.ensure(N)); CU(D.warp_base.ensure((N + 31) / 32));
+    CU(D.rays.ensure(N)); CU(D.ray_sh.ensure(2 * N)); CU(D.far_tf.ensure(N)); CU(D.counts.ensure(N)); CU(D.warp_base.ensure((N + 31) / 32));
     CU(D.block_sums.ensure(nb)); CU(D.used.ensure(N)); CU(D.rgb_f32.ensure(N * 3)); CU(D.depth_f32.ensure(N));
     CU(D.total.ensure(4));
     // u8 outputs: whole-frame contexts keep ONE frame in pixel order on device 0; a sharded context keeps its packed tiles
@@ -542,17 +542,10 @@ static void set_pose(nrf_ctx* c, MarchParams& M, const float intr[4], const floa
   std::memcpy(M.intr, intr, 16);
 }
 
-static int network_grid(nrf_ctx* c, const Device& D, int n_samples) {
-  if (!c->net_grid_ctas_per_sm) {
-    // Resident CTAs per SM: limits are shared memory 227 KB / 36.9 KB = 6, registers 65536 / (128*72) = 7, TMEM
-    // 512 / 64 columns = 8.  (cudaOccupancyMaxActiveBlocksPerMultiprocessor reports 1 for this kernel on the
-    // 580.159 driver although 4-8 CTAs are measurably co-resident.)  Measured best on B200: 4 (profiles/).
-    int occ = 4;
-    if (const char* env = std::getenv("NRF_NET_CTAS_PER_SM")) occ = std::atoi(env);
-    c->net_grid_ctas_per_sm = std::min(std::max(occ, 1), 8);
-  }
+// k_network is persistent: one 1024-thread CTA per SM (8 tile groups), fewer when there are fewer than 8 tiles per SM.
+static int network_grid(nrf_ctx*, const Device& D, int n_samples) {
   const int tiles = (n_samples + NRF_TILE - 1) / NRF_TILE;
-  return std::max(1, std::min(tiles, D.n_sms * c->net_grid_ctas_per_sm));
+  return std::max(1, std::min(D.n_sms, (tiles + 7) / 8));
 }
 
 // Phase A (async): rays + count + scan, then the 8-byte total read-back.
@@ -562,7 +555,8 @@ static int frame_phase_a(nrf_ctx* c, Device& D, const float intr[4], const float
   const int nb = (D.n_local + 127) / 128;
   CU(cudaEventRecord(D.ev[0], D.stream));
   if (D.n_local > 0) {
-    k_rays_count<<<nb, 128, 0, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p);
+    k_rays_count<<<nb, 128, 0, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
+                                          D.ray_sh.p);
     CU(cudaGetLastError());
   }
   k_scan_blocks<<<1, 1024, 0, D.stream>>>(D.block_sums.p, D.n_local > 0 ? nb : 0, D.total.p);
@@ -593,7 +587,7 @@ static int frame_phase_b(nrf_ctx* c, Device& D) {
   }
   CU(cudaEventRecord(D.ev[2], D.stream));
   CU(nrf_launch_network(2, network_grid(c, D, (int)S), D.stream, &D.net, (int)S, D.samples.p, D.sample_ray.p, D.rays.p,
-                        0, nullptr, D.sample_out.p, nullptr));
+                        D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr));
   CU(cudaEventRecord(D.ev[3], D.stream));
   if (D.n_local > 0) {
     Device& D0 = c->devs[0];
@@ -830,8 +824,8 @@ extern "C" int nrf_probe_encode(nrf_ctx* c, int n, const float* positions, uint1
   if (rc) return rc;
   CU(D.enc.ensure((size_t)n * 4));
   if (indices_out) CU(D.idx.ensure((size_t)n * NRF_L * 8));
-  CU(nrf_launch_network(0, std::max(1, std::min((n + 127) / 128, D.n_sms * 8)), D.stream, &D.net, n, pos.p, nullptr,
-                        nullptr, 1, D.enc.p, nullptr, indices_out ? D.idx.p : nullptr));
+  CU(nrf_launch_network(0, network_grid(c, D, n), D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p,
+                        nullptr, indices_out ? D.idx.p : nullptr));
   CU(cudaMemcpyAsync(enc_out, D.enc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, D.stream));
   if (indices_out) CU(cudaMemcpyAsync(indices_out, D.idx.p, (size_t)n * NRF_L * 8 * 4, cudaMemcpyDeviceToHost, D.stream));
   CU(cudaStreamSynchronize(D.stream));
@@ -850,7 +844,7 @@ extern "C" int nrf_probe_network(nrf_ctx* c, int n, const uint16_t* enc, const f
   CU(D.enc.ensure((size_t)n * 4)); CU(o.ensure(n));
   CU(cudaMemcpyAsync(D.enc.p, enc, (size_t)n * 64, cudaMemcpyHostToDevice, D.stream));
   if (impl == 1) CU(nrf_launch_network_simt(D.stream, &D.net, n, D.enc.p, d4.p, o.p));
-  else CU(nrf_launch_network(1, network_grid(c, D, n), D.stream, &D.net, n, nullptr, nullptr, d4.p, 1, D.enc.p, o.p, nullptr));
+  else CU(nrf_launch_network(1, network_grid(c, D, n), D.stream, &D.net, n, nullptr, nullptr, d4.p, nullptr, 1, D.enc.p, o.p, nullptr));
   std::vector<uint2> h(n);
   CU(cudaMemcpyAsync(h.data(), o.p, (size_t)n * 8, cudaMemcpyDeviceToHost, D.stream));
   CU(cudaStreamSynchronize(D.stream));
@@ -869,7 +863,7 @@ extern "C" int nrf_probe_samples(nrf_ctx* c, int n, const float* positions, cons
   if (!rc) rc = upload_vec3_as_float4(D, n, dirs, d4);
   if (rc) return rc;
   CU(o.ensure(n));
-  CU(nrf_launch_network(2, network_grid(c, D, n), D.stream, &D.net, n, p4.p, nullptr, d4.p, 1, nullptr, o.p, nullptr));
+  CU(nrf_launch_network(2, network_grid(c, D, n), D.stream, &D.net, n, p4.p, nullptr, d4.p, nullptr, 1, nullptr, o.p, nullptr));
   std::vector<uint2> h(n);
   CU(cudaMemcpyAsync(h.data(), o.p, (size_t)n * 8, cudaMemcpyDeviceToHost, D.stream));
   CU(cudaStreamSynchronize(D.stream));
@@ -892,13 +886,13 @@ extern "C" int nrf_bench_stage(nrf_ctx* c, int what, int n, int iters, float* ms
   CU(D.enc.ensure((size_t)S * 4));
   const int grid = network_grid(c, D, S);
   if (what == 1)  // produce the features once
-    CU(nrf_launch_network(0, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, 0, D.enc.p, nullptr, nullptr));
+    CU(nrf_launch_network(0, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, nullptr, nullptr));
   cudaEvent_t e0, e1;
   CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
-  CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, 0, D.enc.p, D.sample_out.p, nullptr));
+  CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, D.sample_out.p, nullptr));
   CU(cudaEventRecord(e0, D.stream));
   for (int i = 0; i < iters; ++i)
-    CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, 0, D.enc.p, D.sample_out.p, nullptr));
+    CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, D.sample_out.p, nullptr));
   CU(cudaEventRecord(e1, D.stream));
   CU(cudaEventSynchronize(e1));
   float ms = 0;
@@ -920,10 +914,10 @@ extern "C" int nrf_bench_encode_positions(nrf_ctx* c, int n, const float* positi
   const int grid = network_grid(c, D, n);
   cudaEvent_t e0, e1;
   CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
-  CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr));
+  CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr));
   CU(cudaEventRecord(e0, D.stream));
   for (int i = 0; i < iters; ++i)
-    CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr));
+    CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr));
   CU(cudaEventRecord(e1, D.stream));
   CU(cudaEventSynchronize(e1));
   float ms = 0;

@@ -11,6 +11,7 @@
 //   samples    : float4[S] {u,v,w (position normalised to [0,1]), dt} + float[S] t_after + int[S] ray, in
 //                WARP-INTERLEAVED order: for each 32-ray patch, step k of all its live rays, then step k+1, ...
 //   warp_base  : int[N/32] first sample of each patch
+//   ray_sh     : uint4[2N] the 16 fp16 SH coefficients of every ray's direction
 //   sample_out : uint2[S]  four halves {r,g,b,sigma}
 #pragma once
 #include <cuda_fp16.h>
@@ -27,7 +28,8 @@ struct LevelInfo {
   uint32_t res;     // grid resolution
   float scale;      // exp2f(l*log2(b))*N_min - 1, computed on the HOST (see DESIGN.md numerics contract)
   uint32_t hashed;  // 1 if res^3 > T_l (fast_hash), 0 = dense index
-  uint32_t pad[3];
+  uint32_t pad;
+  const uint32_t* tab;  // first entry of the level (one __half2 = one uint32 per entry): address = tab + index, 1 IMAD.WIDE
 };
 
 struct NetParams {
@@ -57,6 +59,37 @@ struct MarchParams {
 #define ACT_RELU 1
 #define ACT_EXP 2
 #define ACT_SIGMOID 3
+
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
+  return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
+}
+// tcnn kernel_sh degree 4 (spherical_harmonics.h:66-96); in = normalised direction input in [0,1]; 16 halves out.
+// Evaluated once per RAY (k_rays_count) — the reference evaluates it once per sample although the direction is per ray.
+__device__ __forceinline__ void sh4(float i0, float i1, float i2, uint32_t out[8]) {
+  const float x = i0 * 2.f - 1.f, y = i1 * 2.f - 1.f, z = i2 * 2.f - 1.f;
+  const float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
+  float v[16];
+  v[0] = 0.28209479177387814f;
+  v[1] = -0.48860251190291987f * y;
+  v[2] = 0.48860251190291987f * z;
+  v[3] = -0.48860251190291987f * x;
+  v[4] = 1.0925484305920792f * xy;
+  v[5] = -1.0925484305920792f * yz;
+  v[6] = 0.94617469575755997f * z2 - 0.31539156525251999f;
+  v[7] = -1.0925484305920792f * xz;
+  v[8] = 0.54627421529603959f * x2 - 0.54627421529603959f * y2;
+  v[9] = 0.59004358992664352f * y * (-3.0f * x2 + y2);
+  v[10] = 2.8906114426405538f * xy * z;
+  v[11] = 0.45704579946446572f * y * (1.0f - 5.0f * z2);
+  v[12] = 0.3731763325901154f * z * (5.0f * z2 - 3.0f);
+  v[13] = 0.45704579946446572f * x * (1.0f - 5.0f * z2);
+  v[14] = 1.4453057213202769f * z * (x2 - y2);
+  v[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) out[k] = pack_h2(__float2half_rn(v[2 * k]), __float2half_rn(v[2 * k + 1]));
+}
+#endif
 
 // Ray order and sharding.  The image is cut into 32x32-pixel tiles; tile t belongs to shard t % n_shards (round-robin
 // for balance; the reference interleaves single pixels, pixel = NGPU*tid + gpu, render_utils.h:37).
