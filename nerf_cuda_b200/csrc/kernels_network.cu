@@ -146,16 +146,22 @@ __device__ __forceinline__ float2 mul2(float2 v, float w) {
 // Straight-line code, no divergence.  On hashed levels the two x-corners of a cell share an aligned 8-byte slot exactly
 // when x is even (the hash prime for x is 1, grid.h:88): one LDG.64 fetches the slot of the x corner and a LDG.32
 // predicated on "x odd" fetches the x+1 corner when it lives elsewhere; the predicate is the same for all four pairs.
+// Split in two halves so that a caller can put the loads of two levels in flight before blending either:
+//   level_load  : positions -> 8 raw entries (loads issued) + the three fractional weights
+//   level_blend : fp16-accumulated trilinear blend of the 8 entries
+struct LevelTaps {
+  uint32_t raw[8];
+  float w0, w1, w2;
+};
+
 template <bool IDX>
-__device__ __forceinline__ uint32_t encode_level(const LevelInfo& lv, float u0, float u1, float u2, uint32_t* idx_out) {
+__device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float u1, float u2, LevelTaps& T, uint32_t* idx_out) {
   const float p0 = u0 * lv.scale + 0.5f, p1 = u1 * lv.scale + 0.5f, p2 = u2 * lv.scale + 0.5f;  // -fmad=false
   const float f0 = floorf(p0), f1 = floorf(p1), f2 = floorf(p2);
   const uint32_t g0 = (uint32_t)(int)f0, g1 = (uint32_t)(int)f1, g2 = (uint32_t)(int)f2;
-  const float w0 = p0 - f0, w1 = p1 - f1, w2 = p2 - f2;
-  const float o0 = 1.0f - w0, o1 = 1.0f - w1, o2 = 1.0f - w2;
-  const float2 wlo = mul2(make_float2(o0, w0), o1), whi = mul2(make_float2(o0, w0), w1);  // (f0*f1), corner bits 0,1
+  T.w0 = p0 - f0; T.w1 = p1 - f1; T.w2 = p2 - f2;
   const uint32_t* __restrict__ tl = lv.tab;
-  uint32_t e[8], raw[8];
+  uint32_t e[8];
   if (lv.hashed) {
     const uint32_t m = lv.size - 1u;
     const uint32_t hy0 = g1 * 2654435761u, hy1 = hy0 + 2654435761u, hz0 = g2 * 805459861u, hz1 = hz0 + 805459861u;
@@ -173,32 +179,37 @@ __device__ __forceinline__ uint32_t encode_level(const LevelInfo& lv, float u0, 
       uint32_t far = 0;
       if (odd) far = __ldg(tl + e[2 * j + 1]);
       const bool up = e[2 * j] & 1u;
-      raw[2 * j] = up ? q.y : q.x;
-      raw[2 * j + 1] = odd ? far : (up ? q.x : q.y);
+      T.raw[2 * j] = up ? q.y : q.x;
+      T.raw[2 * j + 1] = odd ? far : (up ? q.x : q.y);
     }
   } else {
-    const uint32_t r1 = lv.res, r2 = lv.res * lv.res, T = lv.size;
+    const uint32_t r1 = lv.res, r2 = lv.res * lv.res, Tl = lv.size;
     const uint32_t b = g0 + g1 * r1 + g2 * r2;
     const uint32_t off[4] = {0u, r1, r2, r1 + r2};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const uint32_t a = b + off[j], c = a + 1u;
-      e[2 * j] = min(a, a - T);
-      e[2 * j + 1] = min(c, c - T);
+      e[2 * j] = min(a, a - Tl);
+      e[2 * j + 1] = min(c, c - Tl);
     }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) raw[k] = __ldg(tl + e[k]);
+    for (int k = 0; k < 8; ++k) T.raw[k] = __ldg(tl + e[k]);
   }
   if (IDX && idx_out) {
 #pragma unroll
     for (int k = 0; k < 8; ++k) idx_out[k] = e[k];
   }
-  const float2 w01 = mul2(wlo, o2), w23 = mul2(whi, o2), w45 = mul2(wlo, w2), w67 = mul2(whi, w2);
+}
+
+__device__ __forceinline__ uint32_t level_blend(const LevelTaps& T) {
+  const float o0 = 1.0f - T.w0, o1 = 1.0f - T.w1, o2 = 1.0f - T.w2;
+  const float2 wlo = mul2(make_float2(o0, T.w0), o1), whi = mul2(make_float2(o0, T.w0), T.w1);  // (f0*f1), corner bits 0,1
+  const float2 w01 = mul2(wlo, o2), w23 = mul2(whi, o2), w45 = mul2(wlo, T.w2), w67 = mul2(whi, T.w2);
   const float wk[8] = {w01.x, w01.y, w23.x, w23.y, w45.x, w45.y, w67.x, w67.y};
   __half2 acc = __floats2half2_rn(0.f, 0.f);
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    const float2 v = mul2(__half22float2(*reinterpret_cast<const __half2*>(&raw[k])), wk[k]);
+    const float2 v = mul2(__half22float2(*reinterpret_cast<const __half2*>(&T.raw[k])), wk[k]);
     acc = __hadd2(acc, __floats2half2_rn(v.x, v.y));  // per-component fp16 RN add, as __half +=
   }
   return *reinterpret_cast<uint32_t*>(&acc);
@@ -219,6 +230,52 @@ __device__ __forceinline__ void ld_relu_pack32(uint32_t taddr, uint32_t* packed)
 // MODE 2: fused        (positions -> out), nothing but 8 B per sample leaves the SM  [production path]
 // dirs_mode 0: SH coefficients of the sample's ray from ray_sh[sample_ray[i]] (computed once per ray by k_rays_count)
 // dirs_mode 1: direction input already normalised, rays[i].xyz; SH evaluated here (stage probes)
+//
+// MODE 2 is software-pipelined inside every group: while the tensor core works on a layer of tile j, the group's
+// threads gather 3-4 levels of tile j+8 (the group's next tile).  The gather slices sit in the five MMA waits where no
+// activation registers are live (after L0-lo, L1, V0-lo, V1-lo, V2 were issued), so the MLP's round-trip latency is
+// hidden behind the group's own gather instead of idling 4 of the SM's 32 warps.
+template <int L0, int L1, bool IDX>
+__device__ __forceinline__ void gather_slice(const NetParams& P, const float4& s, uint32_t* f, uint32_t* idx_out) {
+#pragma unroll
+  for (int l = L0; l < L1; ++l) {
+    LevelTaps A;
+    level_load<IDX>(P.lv[l], s.x, s.y, s.z, A, IDX && idx_out ? idx_out + l * 8 : nullptr);
+    f[l] = level_blend(A);
+  }
+}
+
+// Occupancy experiment (not on the frame path): encode-only with THREADS per CTA and MINB CTAs per SM.
+template <int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+k_encode_exp(const __grid_constant__ NetParams P, int n, const float4* __restrict__ samples, uint4* __restrict__ enc_io) {
+  const int n_tiles = (n + NRF_TILE - 1) / NRF_TILE;
+  const int per_cta = (n_tiles + gridDim.x - 1) / gridDim.x;
+  const int t0 = blockIdx.x * per_cta, t1 = min(n_tiles, t0 + per_cta);
+  for (int tile = t0 + (threadIdx.x >> 7); tile < t1; tile += THREADS / 128) {
+    const int i = tile * NRF_TILE + (threadIdx.x & 127);
+    if (i >= n) continue;
+    const float4 s = __ldg(samples + i);
+    uint32_t f[16];
+    gather_slice<0, 8, false>(P, s, f, nullptr);
+    gather_slice<8, 16, false>(P, s, f, nullptr);
+#pragma unroll
+    for (int kc = 0; kc < 4; ++kc)
+      enc_io[(size_t)i * 4 + kc] = make_uint4(f[kc * 4], f[kc * 4 + 1], f[kc * 4 + 2], f[kc * 4 + 3]);
+  }
+}
+extern "C" cudaError_t nrf_launch_encode_exp(int variant, int sms, cudaStream_t stream, const NetParams* P, int n,
+                                             const float4* samples, uint4* enc_io) {
+  switch (variant) {
+    case 0: k_encode_exp<1024, 1><<<sms, 1024, 0, stream>>>(*P, n, samples, enc_io); break;      // 32 warps, 64 regs
+    case 1: k_encode_exp<768, 2><<<sms * 2, 768, 0, stream>>>(*P, n, samples, enc_io); break;    // 48 warps, 40 regs
+    case 2: k_encode_exp<1024, 2><<<sms * 2, 1024, 0, stream>>>(*P, n, samples, enc_io); break;  // 64 warps, 32 regs
+    case 3: k_encode_exp<512, 1><<<sms, 512, 0, stream>>>(*P, n, samples, enc_io); break;        // 16 warps
+    default: k_encode_exp<768, 1><<<sms, 768, 0, stream>>>(*P, n, samples, enc_io); break;       // 24 warps
+  }
+  return cudaGetLastError();
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(NET_THREADS, 1)
 k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__ samples,
@@ -231,10 +288,29 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
 
   const int tid = threadIdx.x, warp = tid >> 5, g = tid >> 7, gt = tid & 127;
   const int n_tiles = (n + NRF_TILE - 1) / NRF_TILE;
-  uint32_t tmem_base = 0, phase = 0;
-  const uint32_t bar = smem_u32(mbars + g);
+  // contiguous chunk of tiles per CTA, interleaved over its 8 groups
+  const int per_cta = (n_tiles + gridDim.x - 1) / gridDim.x;
+  const int t0 = blockIdx.x * per_cta, t1 = min(n_tiles, t0 + per_cta);
 
-  if (MODE != 0) {
+  if (MODE == 0) {
+    for (int tile = t0 + g; tile < t1; tile += NET_GROUPS) {
+      const int i = tile * NRF_TILE + gt;
+      if (i >= n) continue;
+      const float4 s = __ldg(samples + i);
+      uint32_t f[16];
+      uint32_t* io = idx_out ? idx_out + (size_t)i * NRF_L * 8 : nullptr;
+      gather_slice<0, 8, true>(P, s, f, io);
+      gather_slice<8, 16, true>(P, s, f, io);
+#pragma unroll
+      for (int kc = 0; kc < 4; ++kc)
+        enc_io[(size_t)i * 4 + kc] = make_uint4(f[kc * 4], f[kc * 4 + 1], f[kc * 4 + 2], f[kc * 4 + 3]);
+    }
+    return;
+  }
+
+  uint32_t phase = 0;
+  const uint32_t bar = smem_u32(mbars + g);
+  {
     // weights: 20 KB, already in UMMA core-matrix order -> straight copy
     const uint4* src = P.mlp_packed;
     for (int i = tid; i < SMEM_W_BYTES / 16; i += NET_THREADS) reinterpret_cast<uint4*>(sW)[i] = __ldg(src + i);
@@ -247,49 +323,67 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    tmem_base = *tmem_slot;
   }
+  const uint32_t tmem_base = *tmem_slot;
   const uint32_t t_a = tmem_base + (uint32_t)(g * 64);         // A operand columns (lane field 0: the MMA's view)
   const uint32_t t_d = t_a + 32;                                // accumulator columns
   const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;  // this warp's 32 TMEM lanes
   const uint32_t w_addr = smem_u32(sW);
   const int bar_id = 1 + g;
 
-  // contiguous chunk of tiles per CTA, interleaved over its 8 groups
-  const int per_cta = (n_tiles + gridDim.x - 1) / gridDim.x;
-  const int t0 = blockIdx.x * per_cta, t1 = min(n_tiles, t0 + per_cta);
+#define GROUP_SYNC() do { tc_fence_before(); bar_sync_group(bar_id); } while (0)
+#define ISSUE(N_, K_, NFULL_, OFF_, N0_) \
+  do { if (gt == 0) { tc_fence_after(); issue_layer_ts<N_, K_, NFULL_>(t_d, t_a, w_addr + (OFF_), (N0_)); umma_commit(bar); } } while (0)
+#define MMA_WAIT() do { mbar_wait(bar, phase); phase ^= 1; tc_fence_after(); } while (0)
 
-  for (int tile = t0 + g; tile < t1; tile += NET_GROUPS) {
+  // features of the group's first tile (pipeline prologue)
+  uint32_t fn[16];
+  float4 sn = make_float4(0.f, 0.f, 0.f, 0.f);
+  int tile = t0 + g;
+  if (MODE == 2 && tile < t1) {
+    const int i = tile * NRF_TILE + gt;
+    if (i < n) sn = __ldg(samples + i);
+    gather_slice<0, 8, false>(P, sn, fn, nullptr);
+    gather_slice<8, 16, false>(P, sn, fn, nullptr);
+  }
+
+  for (; tile < t1; tile += NET_GROUPS) {
     const int i = tile * NRF_TILE + gt;
     const bool valid = i < n;
-    uint32_t f[16];
-    // ---- features of this thread's sample --------------------------------------------------------------------------
+    // ---- this tile's features -> A operand; next tile's sample position ---------------------------------------------
     if (MODE == 1) {
 #pragma unroll
       for (int kc = 0; kc < 4; ++kc) {
         const uint4 v = valid ? __ldg(enc_io + (size_t)i * 4 + kc) : make_uint4(0, 0, 0, 0);
-        f[kc * 4 + 0] = v.x; f[kc * 4 + 1] = v.y; f[kc * 4 + 2] = v.z; f[kc * 4 + 3] = v.w;
-      }
-    } else {
-      const float4 s = valid ? __ldg(samples + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-      for (int kc = 0; kc < 4; ++kc) {
-#pragma unroll
-        for (int li = 0; li < 4; ++li) {
-          const int l = kc * 4 + li;
-          f[l] = encode_level<MODE == 0>(P.lv[l], s.x, s.y, s.z,
-                                         (MODE == 0 && idx_out && valid) ? idx_out + ((size_t)i * NRF_L + l) * 8 : nullptr);
-        }
-        if (MODE == 0 && valid) enc_io[(size_t)i * 4 + kc] = make_uint4(f[kc * 4], f[kc * 4 + 1], f[kc * 4 + 2], f[kc * 4 + 3]);
+        fn[kc * 4 + 0] = v.x; fn[kc * 4 + 1] = v.y; fn[kc * 4 + 2] = v.z; fn[kc * 4 + 3] = v.w;
       }
     }
-    if (MODE == 0) continue;
-    // ---- density layer 0: 32 -> 64 (two N=32 halves), ReLU ---------------------------------------------------------
-    tmem_st16(t_a + lane_off, f);
+    tmem_st16(t_a + lane_off, fn);
+    const bool has_next = MODE == 2 && tile + NET_GROUPS < t1;   // uniform over the group
+    if (has_next) {
+      const int in = i + NET_GROUPS * NRF_TILE;
+      sn = in < n ? __ldg(samples + in) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     tmem_wait_st();
-    tc_fence_before(); bar_sync_group(bar_id);
-    if (gt == 0) { tc_fence_after(); issue_layer_ts<32, 32, 64>(t_d, t_a, w_addr + W0_OFF, 0); umma_commit(bar); }
-    // SH coefficients of the direction while the MMA runs
+    // ---- density layer 0: 32 -> 64 (two N=32 halves), ReLU ---------------------------------------------------------
+    GROUP_SYNC();
+    ISSUE(32, 32, 64, W0_OFF, 0);
+    if (has_next) gather_slice<0, 4, false>(P, sn, fn, nullptr);
+    uint32_t h[32];
+    MMA_WAIT();
+    ld_relu_pack32(t_d + lane_off, h);
+    GROUP_SYNC();
+    ISSUE(32, 32, 64, W0_OFF, 32);
+    MMA_WAIT();
+    ld_relu_pack32(t_d + lane_off, h + 16);
+    // ---- density layer 1: 64 -> 16, no activation ------------------------------------------------------------------
+    tmem_st16(t_a + lane_off, h);
+    tmem_st16(t_a + 16 + lane_off, h + 16);
+    tmem_wait_st();
+    GROUP_SYNC();
+    ISSUE(16, 64, 16, W1_OFF, 0);
+    if (has_next) gather_slice<4, 7, false>(P, sn, fn, nullptr);
+    // SH coefficients of the direction (per ray)
     uint32_t sh[8];
     if (dirs_mode == 0) {
       uint4 a = make_uint4(0, 0, 0, 0), b = a;
@@ -304,20 +398,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
       if (valid) { const float4 r = __ldg(rays + i); dx = r.x; dy = r.y; dz = r.z; }
       sh4(dx, dy, dz, sh);
     }
-    uint32_t h[32];
-    mbar_wait(bar, phase); phase ^= 1; tc_fence_after();
-    ld_relu_pack32(t_d + lane_off, h);
-    tc_fence_before(); bar_sync_group(bar_id);
-    if (gt == 0) { tc_fence_after(); issue_layer_ts<32, 32, 64>(t_d, t_a, w_addr + W0_OFF, 32); umma_commit(bar); }
-    mbar_wait(bar, phase); phase ^= 1; tc_fence_after();
-    ld_relu_pack32(t_d + lane_off, h + 16);
-    // ---- density layer 1: 64 -> 16, no activation ------------------------------------------------------------------
-    tmem_st16(t_a + lane_off, h);
-    tmem_st16(t_a + 16 + lane_off, h + 16);
-    tmem_wait_st();
-    tc_fence_before(); bar_sync_group(bar_id);
-    if (gt == 0) { tc_fence_after(); issue_layer_ts<16, 64, 16>(t_d, t_a, w_addr + W1_OFF, 0); umma_commit(bar); }
-    mbar_wait(bar, phase); phase ^= 1; tc_fence_after();
+    MMA_WAIT();
     __half sigma;
     {
       uint32_t a[16];
@@ -333,33 +414,36 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     // ---- rgb layer 0: [den16 | sh16] 32 -> 64, ReLU ----------------------------------------------------------------
     tmem_st16(t_a + lane_off, h);
     tmem_wait_st();
-    tc_fence_before(); bar_sync_group(bar_id);
-    if (gt == 0) { tc_fence_after(); issue_layer_ts<32, 32, 64>(t_d, t_a, w_addr + V0_OFF, 0); umma_commit(bar); }
-    mbar_wait(bar, phase); phase ^= 1; tc_fence_after();
+    GROUP_SYNC();
+    ISSUE(32, 32, 64, V0_OFF, 0);
+    if (has_next) gather_slice<7, 10, false>(P, sn, fn, nullptr);
+    MMA_WAIT();
     ld_relu_pack32(t_d + lane_off, h);
-    tc_fence_before(); bar_sync_group(bar_id);
-    if (gt == 0) { tc_fence_after(); issue_layer_ts<32, 32, 64>(t_d, t_a, w_addr + V0_OFF, 32); umma_commit(bar); }
-    mbar_wait(bar, phase); phase ^= 1; tc_fence_after();
+    GROUP_SYNC();
+    ISSUE(32, 32, 64, V0_OFF, 32);
+    MMA_WAIT();
     ld_relu_pack32(t_d + lane_off, h + 16);
     // ---- rgb layer 1: 64 -> 64, ReLU -------------------------------------------------------------------------------
     tmem_st16(t_a + lane_off, h);
     tmem_st16(t_a + 16 + lane_off, h + 16);
     tmem_wait_st();
-    tc_fence_before(); bar_sync_group(bar_id);
-    if (gt == 0) { tc_fence_after(); issue_layer_ts<32, 64, 64>(t_d, t_a, w_addr + V1_OFF, 0); umma_commit(bar); }
-    mbar_wait(bar, phase); phase ^= 1; tc_fence_after();
+    GROUP_SYNC();
+    ISSUE(32, 64, 64, V1_OFF, 0);
+    if (has_next) gather_slice<10, 13, false>(P, sn, fn, nullptr);
+    MMA_WAIT();
     ld_relu_pack32(t_d + lane_off, h);
-    tc_fence_before(); bar_sync_group(bar_id);
-    if (gt == 0) { tc_fence_after(); issue_layer_ts<32, 64, 64>(t_d, t_a, w_addr + V1_OFF, 32); umma_commit(bar); }
-    mbar_wait(bar, phase); phase ^= 1; tc_fence_after();
+    GROUP_SYNC();
+    ISSUE(32, 64, 64, V1_OFF, 32);
+    MMA_WAIT();
     ld_relu_pack32(t_d + lane_off, h + 16);
     // ---- rgb layer 2: 64 -> 16 (3 used), output activation ---------------------------------------------------------
     tmem_st16(t_a + lane_off, h);
     tmem_st16(t_a + 16 + lane_off, h + 16);
     tmem_wait_st();
-    tc_fence_before(); bar_sync_group(bar_id);
-    if (gt == 0) { tc_fence_after(); issue_layer_ts<16, 64, 16>(t_d, t_a, w_addr + V2_OFF, 0); umma_commit(bar); }
-    mbar_wait(bar, phase); phase ^= 1; tc_fence_after();
+    GROUP_SYNC();
+    ISSUE(16, 64, 16, V2_OFF, 0);
+    if (has_next) gather_slice<13, 16, false>(P, sn, fn, nullptr);
+    MMA_WAIT();
     {
       uint32_t a[16];
       tmem_ld16(t_d + lane_off, a);
@@ -372,15 +456,16 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
       }
     }
     // the next tile's first tcgen05.st / MMA of this group must not overtake these TMEM reads
-    tc_fence_before(); bar_sync_group(bar_id);
+    GROUP_SYNC();
   }
+#undef GROUP_SYNC
+#undef ISSUE
+#undef MMA_WAIT
 
-  if (MODE != 0) {
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 0)
-      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
-  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
 }
 
 // ------------------------------------------------------------------------------------------------ SIMT check kernel

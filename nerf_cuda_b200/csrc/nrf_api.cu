@@ -47,6 +47,8 @@ size_t nrf_network_smem_bytes();
 cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t stream, const NetParams* P, int n,
                                const float4* samples, const int* sample_ray, const float4* rays, const uint4* ray_sh,
                                int dirs_mode, uint4* enc_io, uint2* out, uint32_t* idx_out);
+cudaError_t nrf_launch_encode_exp(int variant, int sms, cudaStream_t stream, const NetParams* P, int n,
+                                  const float4* samples, uint4* enc_io);
 cudaError_t nrf_launch_network_simt(cudaStream_t stream, const NetParams* P, int n, const uint4* enc,
                                     const float4* dirs01, uint2* out);
 }
@@ -924,5 +926,27 @@ extern "C" int nrf_bench_encode_positions(nrf_ctx* c, int n, const float* positi
   CU(cudaEventElapsedTime(&ms, e0, e1));
   *ms_out = ms / iters;
   pos.release();
+  return NRF_OK;
+}
+
+// Experiment hook (not in the public header): encode-only occupancy variants on the last frame's samples.
+extern "C" int nrf_exp_encode(nrf_ctx* c, int variant, int iters, float* ms_out) {
+  NEED_MODEL(c);
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  const int S = (int)D.last_samples;
+  if (S <= 0) return fail(NRF_ESTATE, "render a frame first");
+  CU(D.enc.ensure((size_t)S * 4));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+  CU(nrf_launch_encode_exp(variant, D.n_sms, D.stream, &D.net, S, D.samples.p, D.enc.p));
+  CU(cudaEventRecord(e0, D.stream));
+  for (int i = 0; i < iters; ++i) CU(nrf_launch_encode_exp(variant, D.n_sms, D.stream, &D.net, S, D.samples.p, D.enc.p));
+  CU(cudaEventRecord(e1, D.stream));
+  CU(cudaEventSynchronize(e1));
+  float ms = 0;
+  CU(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  *ms_out = ms / iters;
   return NRF_OK;
 }
