@@ -4,11 +4,12 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from nerf_cuda_b200 import NerfRender, synthetic as syn
 cfg = sys.argv[1] if len(sys.argv) > 1 else "C2"
 W = int(sys.argv[2]) if len(sys.argv) > 2 else 400
+H = int(sys.argv[3]) if len(sys.argv) > 3 else W
 sc = syn.make_scene(cfg)
 r = NerfRender(1)
 r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
-r.set_resolution((W, W))
-intr, pose = syn.intrinsics(W, W), syn.look_at_pose(syn.camera_radius(cfg), 20.0, 45.0)
+r.set_resolution((W, H))
+intr, pose = syn.intrinsics(W, H), syn.look_at_pose(syn.camera_radius(cfg), 20.0, 45.0)
 for _ in range(2):
     r.render_frame_device(intr, pose)
 r.synchronize()
