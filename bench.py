@@ -272,10 +272,18 @@ def gpu_arm(args):
         c = cpu_arm(args.workload, steps=2, warmup=1, target_s=4.0)
         out["cpu_baseline"] = {"value": c["value"], "unit": "rays/s", "cores": c["cores"], "kind": "port", "sample": c["sample"]}
     if rank == 0:
-        print(json.dumps(out))
-    r.close()
+        print(json.dumps(out), flush=True)
+    # teardown order matters: every torch tensor that was used on the library's stream must be released (and the
+    # caching allocator's blocks for that stream returned) BEFORE nrf_destroy destroys the stream
+    gatherer = local_rgb = host_frame = frame = timed = None
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
+    torch.cuda.empty_cache()
+    r.close()
 
 
 def main():

@@ -29,6 +29,12 @@ int nrf_stream(nrf_ctx* ctx, void** stream);
  * q = local_tile*1024 + patch*32 + lane, patches of 8x4 pixels, 4x8 patches per tile). */
 int nrf_shard_pixel(nrf_ctx* ctx, int q, int* pixel);
 
+/* Memory micro-benchmarks on device 0 (roofline denominators for the hash gather).  mode 0: coalesced
+ * 16-byte streaming reads over a window (window <= L2 size => L2->SM bandwidth, window >> L2 => HBM read bandwidth);
+ * mode 1: one random 8-byte slot per lane (one 32-byte sector in its own 128-byte line: the access shape of a hashed
+ * grid level).  *gbs = requested bytes per second / 1e9; *gloads (may be NULL) = loads per nanosecond. */
+int nrf_bench_memory(nrf_ctx* ctx, int mode, size_t window_bytes, int iters, float* gbs, float* gloads);
+
 #ifdef __cplusplus
 }
 #endif

@@ -188,6 +188,12 @@ class NerfRender:
         _check(self._l.nrf_bench_stage(self._ctx, what, n, iters, C.byref(ms)))
         return ms.value
 
+    def bench_memory(self, mode, window_bytes, iters=3):
+        """Memory micro-benchmark (nerf_b200_ext.h nrf_bench_memory): returns (GB/s requested, loads per ns)."""
+        g, l = C.c_float(), C.c_float()
+        _check(self._l.nrf_bench_memory(self._ctx, mode, C.c_size_t(window_bytes), iters, C.byref(g), C.byref(l)))
+        return g.value, l.value
+
     # ---- stage probes ---------------------------------------------------------------------------------------------
     def probe_rays(self, cam, pos, W, H, pix0=0, n=None):
         n = W * H - pix0 if n is None else n

@@ -51,6 +51,8 @@ cudaError_t nrf_launch_encode_exp(int variant, int sms, cudaStream_t stream, con
                                   const float4* samples, uint4* enc_io);
 cudaError_t nrf_launch_network_simt(cudaStream_t stream, const NetParams* P, int n, const uint4* enc,
                                     const float4* dirs01, uint2* out);
+cudaError_t nrf_launch_probe(int mode, int sms, cudaStream_t stream, const void* buf, size_t bytes, int work,
+                             uint32_t* sink);
 }
 
 // ---------------------------------------------------------------------------------------------------- errors
@@ -948,5 +950,40 @@ extern "C" int nrf_exp_encode(nrf_ctx* c, int variant, int iters, float* ms_out)
   CU(cudaEventElapsedTime(&ms, e0, e1));
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   *ms_out = ms / iters;
+  return NRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- memory probes
+// Roofline denominators measured on the box (kernels_probe.cu).  mode 0: streaming 16-byte reads over `window_bytes`
+// (<= L2 => L2 bandwidth, >> L2 => HBM); mode 1: one random 8-byte slot (= one 32-byte sector, own 128-byte line) per
+// lane.  *gbs = bytes REQUESTED by the threads per second / 1e9 (mode 1: 8 B per load); *gloads = loads per ns.
+extern "C" int nrf_bench_memory(nrf_ctx* c, int mode, size_t window_bytes, int iters, float* gbs, float* gloads) {
+  if (!c || !gbs || mode < 0 || mode > 1 || window_bytes < (1u << 20) || iters < 1)
+    return fail(NRF_EINVAL, "nrf_bench_memory: bad arguments");
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  void* buf = nullptr;
+  uint32_t* sink = nullptr;
+  CU(cudaMalloc(&buf, window_bytes));
+  CU(cudaMalloc(&sink, 4));
+  CU(cudaMemsetAsync(buf, 0, window_bytes, D.stream));
+  // work per launch: mode 0 = passes over the window (>= ~4 GB read in total), mode 1 = loads per thread
+  const int work = mode == 0 ? (int)std::max<size_t>(1, (4ull << 30) / window_bytes) : 4096;
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+  CU(nrf_launch_probe(mode, D.n_sms, D.stream, buf, window_bytes, work, sink));  // warm-up (fills L2)
+  CU(cudaEventRecord(e0, D.stream));
+  for (int i = 0; i < iters; ++i) CU(nrf_launch_probe(mode, D.n_sms, D.stream, buf, window_bytes, work, sink));
+  CU(cudaEventRecord(e1, D.stream));
+  CU(cudaEventSynchronize(e1));
+  float ms = 0;
+  CU(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(buf); cudaFree(sink);
+  const double s = ms * 1e-3 / iters;
+  const double loads = mode == 0 ? (double)(window_bytes / 16) * work : (double)D.n_sms * 1024.0 * work;
+  const double bytes = loads * (mode == 0 ? 16.0 : 8.0);
+  *gbs = (float)(bytes / s / 1e9);
+  if (gloads) *gloads = (float)(loads / s / 1e9);
   return NRF_OK;
 }

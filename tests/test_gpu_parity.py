@@ -215,3 +215,28 @@ def test_sharded_contexts_assemble_to_the_same_frame(pair):
             assert pq == -1 or 0 <= pq < W * H
         rs.close()
     assert np.array_equal(sh.assemble(g).numpy(), full_u8)
+
+
+def test_two_gpus_one_process_peer_frame(pair):
+    """The reference's own multi-GPU model (one process, NGPU devices, nerf_render.cu:252-253,345-358): with n_gpus=2
+    every device renders its tiles and stores its u8 pixels straight into device 0's frame over NVLink.  The frame must
+    equal the single-GPU frame byte for byte.  Skipped on a one-GPU box."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    name, sc, r, O = pair
+    W, H = 200, 120
+    intr, pose = syn.intrinsics(W, H), syn.look_at_pose(syn.camera_radius(name), 20.0, 210.0)
+    r.set_shard(0, 1)
+    r.set_resolution((W, H))
+    rgb1, dep1 = (a.copy() for a in r.render_frame(intr, pose))
+    f1, d1, c1 = r.float_frame()
+    r2 = NerfRender(2)
+    r2.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    r2.set_resolution((W, H))
+    for _ in range(2):
+        rgb2, dep2 = (a.copy() for a in r2.render_frame(intr, pose))
+    f2, d2, c2 = r2.float_frame()
+    r2.close()
+    assert np.array_equal(rgb1, rgb2) and np.array_equal(dep1, dep2)
+    assert np.array_equal(f1, f2) and np.array_equal(c1, c2)
