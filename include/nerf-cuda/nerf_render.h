@@ -89,9 +89,10 @@ class NerfRender {
   void generate_rays(Camera, const Mat4&, int threadid) {
     if (threadid < 0) throw std::runtime_error("generate_rays: bad thread id");
   }
-  // nerf_render.cu:388-429: dead code in the reference (no caller; the density evaluation inside is commented out at
-  // :415).  The occupancy grid always comes from the snapshot.
-  void generate_density_grid() {}
+  // nerf_render.cu:388-429.  Dead code in the reference (no caller; the density evaluation inside is commented out at
+  // :415); here it does what the code intends: density network at every cell centre of every cascade, x 0.001691,
+  // EMA-max with decay 0.95 from the 1/64 fill, then the occupancy bitfield of the march is rebuilt.
+  void generate_density_grid() { check(nrf_generate_density_grid(ctx_, 0.95f, 1, 0ull, 0, nullptr)); }
 
   nrf_ctx* handle() const { return ctx_; }
   nrf_stats stats() {

@@ -128,6 +128,28 @@ int nrf_get_float_frame(nrf_ctx* ctx, float* rgb_f32, float* depth_f32, int32_t*
 int nrf_get_stats(nrf_ctx* ctx, nrf_stats* out);
 int nrf_synchronize(nrf_ctx* ctx);
 
+/* NerfRender::generate_density_grid (nerf_render.cu:388-429; render_utils.h:79-128 init_xyzs / dd_scale / add_random /
+ * dg_update): re-evaluates the density network at the centre of every occupancy cell of every cascade (jittered by
+ * +-half a cell with pcg32(jitter_seed) when jitter != 0), scales by 0.001691, EMA-max-updates the resident float grid
+ * (grid = max(grid*decay, density) where grid >= 0; reset != 0 starts from the reference's 1/64 fill), then refreshes
+ * mean_density and the occupancy bitfield the march reads.  The reference routine is dead code; see DESIGN.md for the
+ * decisions taken where it is broken.  *mean_density_out (may be NULL) = new mean of the grid. */
+int nrf_generate_density_grid(nrf_ctx* ctx, float decay, int reset, unsigned long long jitter_seed, int jitter,
+                              float* mean_density_out);
+/* Resident float density grid [cascades*H^3] and occupancy bitfield [cascades*H^3/32] (either pointer may be NULL). */
+int nrf_get_density_grid(nrf_ctx* ctx, float* grid_out, uint32_t* bits_out);
+
+/* Frame post-processing on linear RGBA float buffers (CudaRenderBuffer::accumulate / ::tonemap, src/render_buffer.cu:
+ * accumulate_kernel :224-258, tonemap :260-338, tonemap_kernel :529-555; the GL-surface / DLSS output plumbing is not
+ * built — no graphics stack).  All buffers are host pointers to n_pixels*4 floats.  If frame_rgba != NULL the frame is
+ * folded into accum_rgba as the (sample_count+1)-th sample (running mean; colour spaces as EColorSpace, common.h:93-97:
+ * 0 Linear, 1 SRGB, 2 VisPosNeg).  If out_rgba != NULL the accumulator is blended over background_rgba (given in sRGB),
+ * exposed by 2^exposure, tonemapped (ETonemapCurve, common.h:100-105: 0 Identity, 1 ACES, 2 Hable, 3 Reinhard),
+ * converted to output_color_space and optionally clamped to [0,1]. */
+int nrf_postprocess(nrf_ctx* ctx, int n_pixels, const float* frame_rgba, float* accum_rgba, float sample_count,
+                    int color_space, float exposure, const float background_rgba[4], int output_color_space,
+                    int tonemap_curve, int clamp_output, float* out_rgba);
+
 /* ---- stage probes (test / bench entry points; host pointers in, host pointers out) -------------------- */
 
 /* K1-K5 (render_utils.h:31-66,338-392): rays for pixels [pix0, pix0+n). rays_d n*3 (AoS), near/far n. */

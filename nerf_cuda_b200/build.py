@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libnerf_b200.so")
-SOURCES = ["nrf_api.cu", "kernels_exact.cu", "kernels_network.cu", "kernels_composite.cu", "kernels_probe.cu"]
+SOURCES = ["nrf_api.cu", "kernels_exact.cu", "kernels_network.cu", "kernels_composite.cu", "kernels_probe.cu", "kernels_post.cu"]
 HEADERS = ["nrf_device.cuh", "nrf_snapshot.h", "../../include/nerf_b200.h", "../../include/nerf_b200_ext.h",
            "../../include/nerf-cuda/nerf_render.h", "../host/render_server.cpp", "../host/testbed.cpp"]
 # host executables (C++ over the C ABI): the reference's render_server / testbed counterparts

@@ -188,6 +188,32 @@ class NerfRender:
         _check(self._l.nrf_bench_stage(self._ctx, what, n, iters, C.byref(ms)))
         return ms.value
 
+    def generate_density_grid(self, decay=0.95, reset=True, seed=0, jitter=False) -> float:
+        """NerfRender::generate_density_grid (nerf_render.cu:388-429); returns the new mean density."""
+        m = C.c_float()
+        _check(self._l.nrf_generate_density_grid(self._ctx, C.c_float(decay), int(bool(reset)), C.c_ulonglong(seed),
+                                                 int(bool(jitter)), C.byref(m)))
+        return m.value
+
+    def density_grid(self, n_cells: int):
+        """(float grid [n_cells], occupancy bitfield [n_cells/32]) resident on device 0."""
+        g, b = np.zeros(n_cells, np.float32), np.zeros(n_cells // 32, np.uint32)
+        _check(self._l.nrf_get_density_grid(self._ctx, _p(g, C.c_float), _p(b, C.c_uint32)))
+        return g, b
+
+    def postprocess(self, accum, frame=None, sample_count=0.0, color_space=0, exposure=0.0, background=None,
+                    output_color_space=1, tonemap_curve=0, clamp=True, want_output=True):
+        """accumulate + tonemap (render_buffer.cu:224-258,529-555) on RGBA float arrays [n,4]; returns (accum, out)."""
+        accum = np.ascontiguousarray(accum, np.float32).copy()
+        n = accum.shape[0]
+        fr = _f32(frame) if frame is not None else None
+        bg = _f32(background if background is not None else [0, 0, 0, 0])
+        out = np.zeros_like(accum) if want_output else None
+        _check(self._l.nrf_postprocess(self._ctx, n, _p(fr, C.c_float), _p(accum, C.c_float), C.c_float(sample_count),
+                                       color_space, C.c_float(exposure), _p(bg, C.c_float), output_color_space,
+                                       tonemap_curve, int(bool(clamp)), _p(out, C.c_float)))
+        return accum, out
+
     def bench_memory(self, mode, window_bytes, iters=3):
         """Memory micro-benchmark (nerf_b200_ext.h nrf_bench_memory): returns (GB/s requested, loads per ns)."""
         g, l = C.c_float(), C.c_float()

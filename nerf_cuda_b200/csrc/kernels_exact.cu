@@ -326,3 +326,83 @@ extern "C" __global__ void k_cast_half(const float* __restrict__ in, __half* __r
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = __float2half_rn(in[i]);
 }
+
+// ---- density-grid regeneration (NerfRender::generate_density_grid, src/nerf_render.cu:388-429) ---------------------
+// pcg32 (tcnn default_rng_t, random.h:36-65): LCG 6364136223846793005 with stream constant inc, XSH-RR output,
+// O(log n) skip-ahead.  next_float() = bits (u >> 9) | 0x3f800000 minus 1.
+struct Pcg32 {
+  unsigned long long state, inc;
+  __device__ Pcg32(unsigned long long initstate, unsigned long long initseq = 1ull) {
+    state = 0ull; inc = (initseq << 1u) | 1ull;
+    next_uint(); state += initstate; next_uint();
+  }
+  __device__ uint32_t next_uint() {
+    const unsigned long long old = state;
+    state = old * 0x5851f42d4c957f2dull + inc;
+    const uint32_t xorshifted = (uint32_t)(((old >> 18u) ^ old) >> 27u), rot = (uint32_t)(old >> 59u);
+    return (xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31u));
+  }
+  __device__ float next_float() { return __uint_as_float((next_uint() >> 9) | 0x3f800000u) - 1.0f; }
+  __device__ void advance(unsigned long long delta) {
+    unsigned long long cur_mult = 0x5851f42d4c957f2dull, cur_plus = inc, acc_mult = 1ull, acc_plus = 0ull;
+    while (delta > 0) {
+      if (delta & 1ull) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+      cur_plus = (cur_mult + 1ull) * cur_plus;
+      cur_mult *= cur_mult;
+      delta >>= 1;
+    }
+    state = acc_mult * state + acc_plus;
+  }
+};
+
+// Sample positions of one cascade: init_xyzs (render_utils.h:88-105) -> dd_scale by (bound_c - half) (:79-86,
+// nerf_render.cu:411) -> add_random with k = half (:107-117, nerf_render.cu:412; the generator is advanced to the
+// element index, tcnn style, instead of handing every thread the same state) -> normalised to [0,1] like every network
+// input (nerf_render.cu:311-312).  Cell order == the march's cell index ((x*H + y)*H + z, render_utils.h:613-616).
+extern "C" __global__ void k_dg_positions(uint32_t H, float bound_c, float half, float pos_w, unsigned long long seed,
+                                          int jitter, unsigned long long elem0, float4* __restrict__ samples) {
+  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= H * H * H) return;
+  const uint32_t id[3] = {idx / (H * H), idx % (H * H) / H, idx % H};
+  float u[3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    float p = -1.f + 2.f / (H - 1) * id[a];
+    p = (bound_c - half) * p + 0.f;
+    if (jitter) {
+      Pcg32 rng(seed);
+      rng.advance(elem0 + 3ull * idx + a);
+      p += half * (2.f * rng.next_float() - 1.f) + 0.f;
+    }
+    u[a] = pos_w * p + 0.5f;
+  }
+  samples[idx] = make_float4(u[0], u[1], u[2], 0.f);
+}
+
+// dd_scale by 0.001691 (nerf_render.cu:417) + dg_update (render_utils.h:119-128): EMA-max of the decayed grid and the
+// freshly evaluated density (sigma = 4th half of the network output).  Also accumulates the sum for mean_density.
+extern "C" __global__ void k_dg_update(uint32_t n, const uint2* __restrict__ sample_out, float decay, int reset,
+                                       float* __restrict__ grid, double* __restrict__ sum) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  float v = 0.f;
+  if (i < n) {
+    const float sigma = __half2float(__ushort_as_half((unsigned short)(sample_out[i].y >> 16)));
+    const float tmp = 0.001691f * sigma + 0.f;
+    const float dg = reset ? 1.0f / 64 : grid[i];
+    v = dg;
+    if (dg >= 0) v = (dg * decay > tmp) ? dg * decay : tmp;
+    grid[i] = v;
+  }
+  // block sum in double (order-independent enough for a threshold that is clamped to 0.01 anyway)
+  double d = (double)v;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+  __shared__ double ws[32];
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = d;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0;
+    for (uint32_t w = 0; w < (blockDim.x + 31) / 32; ++w) t += ws[w];
+    atomicAdd(sum, t);
+  }
+}

@@ -39,6 +39,12 @@ __global__ void k_emit(const MarchParams P, int n, const float4* rays, const flo
                        float* dbg, const long long* dbg_offsets, long long capacity);
 __global__ void k_build_occupancy(const float* grid, uint32_t n_cells, float thresh, uint32_t* bits);
 __global__ void k_cast_half(const float* in, __half* out, size_t n);
+__global__ void k_accumulate(int n, const float4* frame, float4* accum, float sample_count, int color_space);
+__global__ void k_tonemap(int n, const float4* accum, float exposure, float4 background, int color_space,
+                          int output_color_space, int curve, int clamp_output, float4* out);
+__global__ void k_dg_positions(uint32_t H, float bound_c, float half, float pos_w, unsigned long long seed, int jitter,
+                               unsigned long long elem0, float4* samples);
+__global__ void k_dg_update(uint32_t n, const uint2* sample_out, float decay, int reset, float* grid, double* sum);
 __global__ void k_composite(int n_rays, ShardMap map, const int* warp_base, const int* counts, const float4* rays,
                             const float2* far_tf, const float4* samples, const float* t_after, const uint2* sample_out,
                             float* rgb_f32, float* depth_f32, int* used_counts, uint8_t* rgb_u8, uint8_t* depth_u8,
@@ -192,6 +198,7 @@ struct Device {
   DevBuf<__half> params_h;     // all params as fp16 (mlp row-major 10240 | table)
   DevBuf<uint4> mlp_packed;    // 1280 x 16 B
   DevBuf<uint32_t> occupancy;
+  DevBuf<float> density_grid;  // float grid [C*H^3], kept for generate_density_grid's EMA update
   DevBuf<float> div_lut;
   NetParams net{};
   MarchParams march{};
@@ -264,7 +271,7 @@ extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
 
 static void free_device(Device& D) {
   cudaSetDevice(D.dev);
-  D.params_h.release(); D.mlp_packed.release(); D.occupancy.release(); D.div_lut.release();
+  D.params_h.release(); D.mlp_packed.release(); D.occupancy.release(); D.density_grid.release(); D.div_lut.release();
   D.rays.release(); D.ray_sh.release(); D.samples.release(); D.far_tf.release(); D.t_after.release(); D.rgb_f32.release();
   D.depth_f32.release(); D.counts.release(); D.warp_base.release(); D.block_sums.release();
   D.sample_ray.release(); D.used.release(); D.sample_out.release(); D.rgb_u8.release(); D.depth_u8.release();
@@ -290,8 +297,7 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
   CU(cudaSetDevice(D.dev));
   const nrf_model_desc& d = c->desc;
   DevBuf<float> tmp;
-  const size_t chunk = std::max(n_params, n_grid);
-  CU(tmp.ensure(chunk));
+  CU(tmp.ensure(n_params));
   CU(D.params_h.ensure(n_params));
   CU(cudaMemcpyAsync(tmp.p, params, n_params * sizeof(float), cudaMemcpyHostToDevice, D.stream));
   k_cast_half<<<(unsigned)((n_params + 255) / 256), 256, 0, D.stream>>>(tmp.p, D.params_h.p, n_params);
@@ -299,8 +305,9 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
   CU(cudaStreamSynchronize(D.stream));
   // occupancy
   CU(D.occupancy.ensure(n_grid / 32));
-  CU(cudaMemcpyAsync(tmp.p, grid, n_grid * sizeof(float), cudaMemcpyHostToDevice, D.stream));
-  k_build_occupancy<<<(unsigned)((n_grid + 255) / 256), 256, 0, D.stream>>>(tmp.p, (uint32_t)n_grid,
+  CU(D.density_grid.ensure(n_grid));
+  CU(cudaMemcpyAsync(D.density_grid.p, grid, n_grid * sizeof(float), cudaMemcpyHostToDevice, D.stream));
+  k_build_occupancy<<<(unsigned)((n_grid + 255) / 256), 256, 0, D.stream>>>(D.density_grid.p, (uint32_t)n_grid,
                                                                           fminf(0.01f, d.mean_density), D.occupancy.p);
   CU(cudaGetLastError());
   // packed MLP weights
@@ -985,5 +992,108 @@ extern "C" int nrf_bench_memory(nrf_ctx* c, int mode, size_t window_bytes, int i
   const double bytes = loads * (mode == 0 ? 16.0 : 8.0);
   *gbs = (float)(bytes / s / 1e9);
   if (gloads) *gloads = (float)(loads / s / 1e9);
+  return NRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- density grid
+// NerfRender::generate_density_grid (nerf_render.cu:388-429; dead code in the reference: no caller, the density call
+// is commented out at :415 and only the last cascade's values would reach dg_update).  Built here as the code intends:
+// per cascade, evaluate the density network at the (optionally jittered) centre of every cell, scale by 0.001691,
+// EMA-max into the float grid (dg_update), then refresh mean_density and the occupancy bitfield the march reads.
+// Decisions: positions are normalised to [0,1] like every other network input; density = sigma after the
+// configured activation; jitter uses pcg32(seed) advanced to the element index (3*(cascade*H^3 + cell) + axis);
+// reset != 0 starts from the reference's 1/64 fill (:395), else from the resident grid.
+extern "C" int nrf_generate_density_grid(nrf_ctx* c, float decay, int reset, unsigned long long jitter_seed, int jitter,
+                                         float* mean_density_out) {
+  NEED_MODEL(c);
+  const nrf_model_desc& d = c->desc;
+  const uint32_t H = d.grid_size, H3 = H * H * H;
+  float mean = 0.f;
+  for (size_t g = 0; g < c->devs.size(); ++g) {
+    Device& D = c->devs[g];
+    CU(cudaSetDevice(D.dev));
+    CU(D.samples.ensure(H3)); CU(D.sample_out.ensure(H3)); CU(D.sample_ray.ensure(H3)); CU(D.t_after.ensure(H3));
+    CU(D.ray_sh.ensure(2));
+    DevBuf<double> sum;
+    CU(sum.ensure(1));
+    CU(cudaMemsetAsync(sum.p, 0, sizeof(double), D.stream));
+    CU(cudaMemsetAsync(D.sample_ray.p, 0, (size_t)H3 * sizeof(int), D.stream));   // every sample "belongs" to ray 0
+    CU(cudaMemsetAsync(D.ray_sh.p, 0, 2 * sizeof(uint4), D.stream));              // direction features: irrelevant to sigma
+    for (uint32_t cas = 0; cas < d.cascades; ++cas) {
+      const float bound_c = (float)(1u << cas) < d.bound ? (float)(1u << cas) : d.bound;  // nerf_render.cu:408
+      const float half = bound_c / H;                                                      // :409
+      k_dg_positions<<<(H3 + 255) / 256, 256, 0, D.stream>>>(H, bound_c, half, D.march.pos_w, jitter_seed, jitter,
+                                                           3ull * cas * H3, D.samples.p);
+      CU(cudaGetLastError());
+      CU(nrf_launch_network(2, network_grid(c, D, (int)H3), D.stream, &D.net, (int)H3, D.samples.p, D.sample_ray.p,
+                            D.rays.p, D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr));
+      k_dg_update<<<(H3 + 255) / 256, 256, 0, D.stream>>>(H3, D.sample_out.p, decay, reset,
+                                                        D.density_grid.p + (size_t)cas * H3, sum.p);
+      CU(cudaGetLastError());
+    }
+    double hsum = 0;
+    CU(cudaMemcpyAsync(&hsum, sum.p, sizeof(double), cudaMemcpyDeviceToHost, D.stream));
+    CU(cudaStreamSynchronize(D.stream));
+    mean = (float)(hsum / ((double)H3 * d.cascades));
+    k_build_occupancy<<<(unsigned)(((size_t)H3 * d.cascades + 255) / 256), 256, 0, D.stream>>>(
+        D.density_grid.p, (uint32_t)((size_t)H3 * d.cascades), fminf(0.01f, mean), D.occupancy.p);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(D.stream));
+    sum.release();
+    D.last_samples = 0;  // the per-frame sample buffers were used as scratch
+  }
+  c->desc.mean_density = mean;
+  if (mean_density_out) *mean_density_out = mean;
+  return NRF_OK;
+}
+
+// Resident float density grid [cascades*H^3] and occupancy bitfield [cascades*H^3/32] of device 0 (either may be NULL).
+extern "C" int nrf_get_density_grid(nrf_ctx* c, float* grid_out, uint32_t* bits_out) {
+  NEED_MODEL(c);
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  const size_t n = (size_t)c->desc.grid_size * c->desc.grid_size * c->desc.grid_size * c->desc.cascades;
+  if (grid_out) CU(cudaMemcpyAsync(grid_out, D.density_grid.p, n * sizeof(float), cudaMemcpyDeviceToHost, D.stream));
+  if (bits_out) CU(cudaMemcpyAsync(bits_out, D.occupancy.p, n / 32 * sizeof(uint32_t), cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaStreamSynchronize(D.stream));
+  return NRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- post-process
+// CudaRenderBuffer::accumulate + ::tonemap (src/render_buffer.cu:598-640 -> accumulate_kernel :224, tonemap_kernel :529)
+// on linear RGBA float buffers.  Host pointers in / out (n_pixels * 4 floats each); accum is read and updated.
+// frame may be NULL (tonemap only); out may be NULL (accumulate only).
+extern "C" int nrf_postprocess(nrf_ctx* c, int n_pixels, const float* frame_rgba, float* accum_rgba, float sample_count,
+                               int color_space, float exposure, const float background_rgba[4], int output_color_space,
+                               int tonemap_curve, int clamp_output, float* out_rgba) {
+  if (!c || n_pixels < 0 || !accum_rgba) return fail(NRF_EINVAL, "nrf_postprocess: bad arguments");
+  if (color_space < 0 || color_space > 2 || output_color_space < 0 || output_color_space > 2 || tonemap_curve < 0 || tonemap_curve > 3)
+    return fail(NRF_EINVAL, "nrf_postprocess: bad colour space / tonemap curve");
+  if (out_rgba && !background_rgba) return fail(NRF_EINVAL, "nrf_postprocess: background required for tonemapping");
+  if (n_pixels == 0) return NRF_OK;
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  DevBuf<float4> f, a, o;
+  const size_t bytes = (size_t)n_pixels * 16;
+  CU(a.ensure(n_pixels));
+  CU(cudaMemcpyAsync(a.p, accum_rgba, bytes, cudaMemcpyHostToDevice, D.stream));
+  const int nb = (n_pixels + 255) / 256;
+  if (frame_rgba) {
+    CU(f.ensure(n_pixels));
+    CU(cudaMemcpyAsync(f.p, frame_rgba, bytes, cudaMemcpyHostToDevice, D.stream));
+    k_accumulate<<<nb, 256, 0, D.stream>>>(n_pixels, f.p, a.p, sample_count, color_space);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(accum_rgba, a.p, bytes, cudaMemcpyDeviceToHost, D.stream));
+  }
+  if (out_rgba) {
+    CU(o.ensure(n_pixels));
+    const float4 bg = make_float4(background_rgba[0], background_rgba[1], background_rgba[2], background_rgba[3]);
+    k_tonemap<<<nb, 256, 0, D.stream>>>(n_pixels, a.p, exposure, bg, color_space, output_color_space, tonemap_curve,
+                                       clamp_output, o.p);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(out_rgba, o.p, bytes, cudaMemcpyDeviceToHost, D.stream));
+  }
+  CU(cudaStreamSynchronize(D.stream));
+  f.release(); a.release(); o.release();
   return NRF_OK;
 }

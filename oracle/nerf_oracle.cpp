@@ -568,6 +568,154 @@ void orc_to_u8(const float* in, uint8_t* out, size_t n) {
   }
 }
 
+// ---- density-grid regeneration: NerfRender::generate_density_grid, nerf_render.cu:388-429, with the kernels it
+// launches: init_xyzs render_utils.h:88-105, dd_scale :79-86, add_random :107-117, dg_update :119-128.  The reference
+// routine is dead code (no caller; the density evaluation is commented out at nerf_render.cu:415), so this restates
+// what the code intends, with the decisions listed in DESIGN.md: positions normalised to [0,1] (nerf_render.cu:311-312)
+// before the network, density = sigma after the configured activation, scale 0.001691 (:417), pcg32 jitter advanced to
+// the element index 3*(cascade*H^3 + cell) + axis (tcnn random.h:36-65 generator; pcg32 skip-ahead), reset = the 1/64
+// fill of :395.  grid [cascades*H^3] is updated in place; returns the new mean density.
+struct Pcg32 {
+  uint64_t state, inc;
+  explicit Pcg32(uint64_t initstate, uint64_t initseq = 1) {
+    state = 0; inc = (initseq << 1u) | 1u;
+    next_uint(); state += initstate; next_uint();
+  }
+  uint32_t next_uint() {
+    const uint64_t old = state;
+    state = old * 0x5851f42d4c957f2dULL + inc;
+    const uint32_t xs = (uint32_t)(((old >> 18u) ^ old) >> 27u), rot = (uint32_t)(old >> 59u);
+    return (xs >> rot) | (xs << ((~rot + 1u) & 31));
+  }
+  float next_float() {
+    const uint32_t b = (next_uint() >> 9) | 0x3f800000u;
+    float f; std::memcpy(&f, &b, 4);
+    return f - 1.0f;
+  }
+  void advance(uint64_t delta) {
+    uint64_t cur_mult = 0x5851f42d4c957f2dULL, cur_plus = inc, acc_mult = 1, acc_plus = 0;
+    while (delta > 0) {
+      if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+      cur_plus = (cur_mult + 1) * cur_plus;
+      cur_mult *= cur_mult;
+      delta >>= 1;
+    }
+    state = acc_mult * state + acc_plus;
+  }
+};
+
+float orc_density_grid(const nrf_model_desc* desc, const uint16_t* mlp_weights, const uint16_t* table, float decay,
+                       int reset, uint64_t seed, int jitter, float* grid) {
+  if (check_arch(*desc)) return -1.f;
+  Levels lv;
+  build_levels(*desc, lv, nullptr);
+  const Mlp m = mlp_view(mlp_weights);
+  const uint32_t H = desc->grid_size, H3 = H * H * H;
+  const float pos_w = (float)(1.0 / (2 * desc->bound));
+  double sum = 0;
+  for (uint32_t cas = 0; cas < desc->cascades; ++cas) {
+    const float bound_c = (float)(1u << cas) < desc->bound ? (float)(1u << cas) : desc->bound;
+    const float half = bound_c / H;
+#pragma omp parallel for schedule(static) reduction(+ : sum)
+    for (long long idx = 0; idx < (long long)H3; ++idx) {
+      const uint32_t id[3] = {(uint32_t)idx / (H * H), (uint32_t)idx % (H * H) / H, (uint32_t)idx % H};
+      float u[3];
+      for (int a = 0; a < 3; ++a) {
+        float p = -1.f + 2.f / (H - 1) * id[a];
+        p = (bound_c - half) * p + 0.f;
+        if (jitter) {
+          Pcg32 rng(seed);
+          rng.advance(3ull * cas * H3 + 3ull * (uint64_t)idx + a);
+          p += half * (2.f * rng.next_float() - 1.f) + 0.f;
+        }
+        u[a] = pos_w * p + 0.5f;
+      }
+      uint16_t enc[32], sh[16] = {0};
+      float out[4];
+      encode_sample(lv, 16, table, u, enc, nullptr);
+      network_sample(*desc, m, enc, sh, out);
+      const float tmp = 0.001691f * out[3] + 0.f;
+      float* g = grid + (size_t)cas * H3 + idx;
+      const float dg = reset ? 1.0f / 64 : *g;
+      float v = dg;
+      if (dg >= 0) v = (dg * decay > tmp) ? dg * decay : tmp;
+      *g = v;
+      sum += (double)v;
+    }
+  }
+  return (float)(sum / ((double)H3 * desc->cascades));
+}
+
+// ---- post-process: src/render_buffer.cu accumulate_kernel :224-258, tonemap :260-338, tonemap_kernel :529-555;
+// linear_to_srgb / srgb_to_linear include/nerf-cuda/common_device.cuh:38-60.  RGBA float buffers, n pixels.
+static inline float srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : std::pow((s + 0.055f) / 1.055f, 2.4f); }
+static inline float linear_to_srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * std::pow(l, 0.41666f) - 0.055f; }
+
+void orc_accumulate(int n, const float* frame, float* accum, float sample_count, int color_space) {
+  for (int i = 0; i < n; ++i) {
+    float c[4], *t = accum + (size_t)i * 4;
+    std::memcpy(c, frame + (size_t)i * 4, 16);
+    if (color_space == 2) {  // VisPosNeg
+      const float val = c[0] - c[1];
+      float tv = t[0] - t[1];
+      tv = (tv * sample_count + val) / (sample_count + 1);
+      t[0] = fmaxf(tv, 0.0f);
+      t[1] = fmaxf(-tv, 0.0f);
+    } else {
+      if (color_space == 1) for (int k = 0; k < 3; ++k) c[k] = linear_to_srgb(c[k]);
+      for (int k = 0; k < 3; ++k) t[k] = (t[k] * sample_count + c[k]) / (sample_count + 1);
+    }
+    t[3] = (t[3] * sample_count + c[3]) / (sample_count + 1);
+  }
+}
+
+static void tonemap_curve(float x[3], int curve) {
+  if (curve == 0) return;
+  for (int k = 0; k < 3; ++k) x[k] = fmaxf(x[k], 0.f);
+  float k0, k1, k2, k3, k4, k5;
+  if (curve == 1) {
+    k0 = 0.6f * 0.6f * 2.51f; k1 = 0.6f * 0.03f; k2 = 0.0f; k3 = 0.6f * 0.6f * 2.43f; k4 = 0.6f * 0.59f; k5 = 0.14f;
+  } else if (curve == 2) {
+    const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
+    k0 = A * F - A * E; k1 = C * B * F - B * E; k2 = 0.0f; k3 = A * F; k4 = B * F; k5 = D * F * F;
+    const float W = 11.2f;
+    const float nom = k0 * (W * W) + k1 * W + k2, denom = k3 * (W * W) + k4 * W + k5;
+    const float white_scale = denom / nom;
+    k0 = 4.0f * k0 * white_scale; k1 = 2.0f * k1 * white_scale; k2 = k2 * white_scale; k3 = 4.0f * k3; k4 = 2.0f * k4;
+  } else {
+    const float Y = 0.2126f * x[0] + (0.7152f * x[1] + 0.0722f * x[2]);
+    const float s = 1.f / (Y + 1.0f);
+    for (int k = 0; k < 3; ++k) x[k] *= s;
+    return;
+  }
+  for (int k = 0; k < 3; ++k) {
+    const float v = x[k], sq = v * v;
+    const float nom = sq * k0 + k1 * v + k2, denom = k3 * sq + k4 * v + k5;
+    x[k] = nom / denom;
+  }
+}
+
+void orc_tonemap(int n, const float* accum, float exposure, const float background_in[4], int color_space,
+                 int output_color_space, int curve, int clamp_output, float* out) {
+  float bg[4];
+  std::memcpy(bg, background_in, 16);
+  if (color_space != 1) for (int k = 0; k < 3; ++k) bg[k] = srgb_to_linear(bg[k]);
+  for (int i = 0; i < n; ++i) {
+    float c[4];
+    std::memcpy(c, accum + (size_t)i * 4, 16);
+    const float weight = (1 - c[3]) * bg[3];
+    for (int k = 0; k < 3; ++k) c[k] += bg[k] * weight;
+    c[3] += weight;
+    if (color_space == 1) for (int k = 0; k < 3; ++k) c[k] = srgb_to_linear(c[k]);
+    const float e = std::pow(2.0f, exposure);
+    for (int k = 0; k < 3; ++k) c[k] *= e;
+    tonemap_curve(c, curve);
+    if (output_color_space == 1) for (int k = 0; k < 3; ++k) c[k] = linear_to_srgb(c[k]);
+    if (clamp_output) for (int k = 0; k < 4; ++k) c[k] = fminf(fmaxf(c[k], 0.0f), 1.0f);
+    std::memcpy(out + (size_t)i * 4, c, 16);
+  }
+}
+
 int orc_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();
@@ -577,3 +725,10 @@ int orc_num_threads(void) {
 }
 
 }  // extern "C"
+
+// pcg32 stream for known-answer tests (tests/test_oracle_golden.py): n outputs after `skip` advance steps.
+extern "C" void orc_pcg32(uint64_t initstate, uint64_t initseq, uint64_t skip, int n, uint32_t* out) {
+  Pcg32 r(initstate, initseq);
+  if (skip) r.advance(skip);
+  for (int i = 0; i < n; ++i) out[i] = r.next_uint();
+}

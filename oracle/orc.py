@@ -123,6 +123,16 @@ class Oracle:
         assert rc == 0
         return out
 
+    def density_grid(self, decay=0.95, reset=True, seed=0, jitter=False, grid=None):
+        """generate_density_grid restatement: returns (new float grid [C*H^3], mean density)."""
+        g = np.ascontiguousarray(self.grid if grid is None else grid, np.float32).copy()
+        self.l.orc_density_grid.restype = C.c_float
+        mean = self.l.orc_density_grid(C.byref(self.desc), _p(self.mlp, C.c_uint16), _p(self.table, C.c_uint16),
+                                       C.c_float(decay), int(bool(reset)), C.c_uint64(seed), int(bool(jitter)),
+                                       _p(g, C.c_float))
+        assert mean >= 0
+        return g, float(mean)
+
     def render(self, intr, pose, W, H, pix0=0, npix=None):
         npix = W * H - pix0 if npix is None else npix
         rgb, depth = np.zeros((npix, 3), np.float32), np.zeros(npix, np.float32)

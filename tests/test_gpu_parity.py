@@ -240,3 +240,93 @@ def test_two_gpus_one_process_peer_frame(pair):
     r2.close()
     assert np.array_equal(rgb1, rgb2) and np.array_equal(dep1, dep2)
     assert np.array_equal(f1, f2) and np.array_equal(c1, c2)
+
+
+def _small_grid_scene(bound, cascades, grid_size=32):
+    d = syn.make_desc(14, bound, cascades, grid_size=grid_size)
+    scene = "sphere" if cascades == 1 else "unbounded"
+    return syn.Scene(d, syn.random_params(d, 1337, 1.0), syn.occupancy_grid(d, scene), syn.aabb_of(d), "small")
+
+
+@pytest.mark.parametrize("bound,cascades", [(1.0, 1), (16.0, 5)])
+def test_density_grid_regeneration(built_lib, bound, cascades):
+    """generate_density_grid (nerf_render.cu:388-429) on the device against the oracle restatement: float grid within
+    the per-sample sigma tolerance (fp16 MLP), occupancy bits identical wherever the density is not within tolerance
+    of the threshold, and the march really uses the rebuilt bitfield."""
+    sc = _small_grid_scene(bound, cascades)
+    n = sc.grid.size
+    r = NerfRender(1)
+    r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
+    g0, b0 = r.density_grid(n)
+    assert np.array_equal(g0, sc.grid)
+    assert np.array_equal(np.unpackbits(b0.view(np.uint8), bitorder="little").astype(bool), sc.grid > 0.01)
+    go = sc.grid
+    for step, (reset, jitter, seed) in enumerate([(True, True, 99), (None, None, None), (False, False, 0), (False, True, 7)]):
+        if step == 1:   # restore the analytic grid after the reset step
+            r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+            go = sc.grid
+            continue
+        mean = r.generate_density_grid(0.95, reset=reset, seed=seed, jitter=jitter)
+        g, b = r.density_grid(n)
+        go, mo = O.density_grid(0.95, reset=reset, seed=seed, jitter=jitter, grid=go)
+        assert np.all(np.abs(g - go) <= REL_TOL * np.maximum(np.abs(go), 1e-6)), (step, np.abs(g - go).max())
+        assert abs(mean - mo) <= REL_TOL * mo
+        thresh = min(0.01, mo)
+        occ = np.unpackbits(b.view(np.uint8), bitorder="little").astype(bool)
+        clear = np.abs(go - thresh) > 2 * REL_TOL * thresh
+        assert np.array_equal(occ[clear], (go > thresh)[clear])
+        assert np.array_equal(occ, g > min(0.01, mean))      # the bitfield is exactly the device grid thresholded
+    assert 0 < occ.sum() < n                                   # a non-trivial occupancy: decayed scene + fresh densities
+    # the march now reads the regenerated bitfield: traversal must match the oracle run on the DEVICE's grid and mean
+    g, _ = r.density_grid(n)
+    d2 = syn.ModelDesc.from_buffer_copy(sc.desc)
+    d2.mean_density = mean
+    O2 = orc.Oracle(d2, sc.params, g, sc.aabb)
+    W = H = 48
+    intr, pose = syn.intrinsics(W, H), syn.look_at_pose(12.0 if cascades > 1 else 4.0, 20.0, 60.0)
+    o, dirs, nears, fars = O2.rays(intr, pose, W, H)
+    cnt_o, smp_o = O2.march(o, dirs, nears, fars)
+    cnt, smp = r.probe_march(o, dirs, nears, fars)
+    assert np.array_equal(cnt, cnt_o) and np.array_equal(bits(smp), bits(smp_o))
+    r.set_resolution((W, H))
+    r.render_frame(intr, pose)
+    rgb, depth, counts = r.float_frame()
+    rgb_o, depth_o, counts_o = O2.render(intr, pose, W, H)
+    assert np.abs(counts - counts_o).max() <= 2   # early termination (T < 1e-4) may flip by a sample under the sigma tolerance
+    assert np.abs(rgb - rgb_o.reshape(rgb.shape)).max() <= IMG_TOL
+    r.close()
+
+
+@pytest.mark.parametrize("color_space,out_space,curve", [(0, 1, 0), (0, 1, 1), (1, 1, 2), (0, 0, 3), (2, 0, 0), (1, 0, 1)])
+def test_postprocess_accumulate_and_tonemap(pair, color_space, out_space, curve):
+    """accumulate_kernel + tonemap_kernel (src/render_buffer.cu:224-258,529-555) on linear buffers against the CPU
+    restatement of the same per-pixel math.  fp32 throughout; powf differs from libm by a few ulp => 2e-6 absolute on
+    values in [0,1], relative beyond."""
+    import ctypes as C
+    name, sc, r, O = pair
+    rng = np.random.default_rng(5)
+    n = 1000 + 37                                      # ragged: not a multiple of the block size
+    frame = rng.uniform(-0.1, 1.6, (n, 4)).astype(np.float32)
+    frame[:, 3] = rng.uniform(0, 1, n).astype(np.float32)
+    frame[:8] = [[0, 0, 0, 0]] * 4 + [[1, 1, 1, 1]] * 2 + [[0.0031308, 0.04045, 0.5, 0.5]] * 2   # branch points
+    accum = rng.uniform(0, 1, (n, 4)).astype(np.float32)
+    bg = np.array([0.2, 0.5, 0.9, 1.0], np.float32)
+    l = orc.lib()
+    fp = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))
+    acc_o = accum.copy()
+    out_o = np.zeros_like(accum)
+    for spp in (0.0, 1.0, 2.0):
+        l.orc_accumulate(n, fp(frame), fp(acc_o), C.c_float(spp), color_space)
+    l.orc_tonemap(n, fp(acc_o), C.c_float(0.7), fp(bg), color_space, out_space, curve, 1, fp(out_o))
+    acc_g = accum
+    for spp in (0.0, 1.0, 2.0):
+        acc_g, out_g = r.postprocess(acc_g, frame, spp, color_space, 0.7, bg, out_space, curve, True)
+    assert np.all(np.abs(acc_g - acc_o) <= 2e-6 + 2e-6 * np.abs(acc_o))
+    assert np.all(np.abs(out_g - out_o) <= 2e-6 + 2e-6 * np.abs(out_o))
+    # tonemap only (frame = NULL), unclamped
+    out_o2 = np.zeros_like(accum)
+    l.orc_tonemap(n, fp(acc_o), C.c_float(-1.0), fp(bg), color_space, out_space, curve, 0, fp(out_o2))
+    _, out_g2 = r.postprocess(acc_o, None, 0.0, color_space, -1.0, bg, out_space, curve, False)
+    assert np.all(np.abs(out_g2 - out_o2) <= 2e-6 + 4e-6 * np.abs(out_o2))
+    assert r.postprocess(np.zeros((0, 4), np.float32), None)[1].shape == (0, 4)

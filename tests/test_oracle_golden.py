@@ -18,6 +18,7 @@ sys.path.insert(0, os.path.join(HERE, "golden"))
 
 import make_golden  # noqa: E402  (shares golden_inputs with the generator)
 from oracle import orc  # noqa: E402
+from nerf_cuda_b200 import synthetic as syn  # noqa: E402
 
 
 def bits(a):
@@ -95,3 +96,42 @@ def test_u8_conversion():
     import ctypes as C
     O.orc_to_u8(v.ctypes.data_as(C.POINTER(C.c_float)), out.ctypes.data_as(C.POINTER(C.c_uint8)), C.c_size_t(v.size))
     assert out.tolist() == [0, 127, 254, 255, 255, 0, 0, 1]
+
+
+def test_pcg32_known_answers():
+    """pcg32 (tcnn default_rng_t, used by the density-grid jitter): the published demo stream of the PCG reference
+    implementation (seed 42, sequence 54) and skip-ahead == stepping."""
+    import ctypes as C
+    l = orc.lib()
+    out = np.zeros(6, np.uint32)
+    l.orc_pcg32(C.c_uint64(42), C.c_uint64(54), C.c_uint64(0), 6, out.ctypes.data_as(C.POINTER(C.c_uint32)))
+    assert [hex(v) for v in out] == ["0xa15c02b7", "0x7b47f409", "0xba1d3330", "0x83d2f293", "0xbfa4784b", "0xcbed606e"]
+    a, b = np.zeros(40, np.uint32), np.zeros(8, np.uint32)
+    l.orc_pcg32(C.c_uint64(1337), C.c_uint64(1), C.c_uint64(0), 40, a.ctypes.data_as(C.POINTER(C.c_uint32)))
+    l.orc_pcg32(C.c_uint64(1337), C.c_uint64(1), C.c_uint64(32), 8, b.ctypes.data_as(C.POINTER(C.c_uint32)))
+    assert np.array_equal(a[32:], b)
+
+
+def test_density_grid_oracle_properties():
+    """generate_density_grid restatement (nerf_render.cu:388-429): reset starts from 1/64, the update is an EMA-max,
+    cells marked negative are left alone, and cell centres are what the march's cell index addresses."""
+    d = syn.make_desc(14, 1.0, 1, grid_size=16)
+    sc = syn.Scene(d, syn.random_params(d, 1337, 1.0), syn.occupancy_grid(d, "sphere"), syn.aabb_of(d))
+    O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
+    g1, m1 = O.density_grid(0.95, reset=True)
+    assert np.all(g1 >= np.float32(1.0 / 64) * np.float32(0.95)) and abs(m1 - g1.mean()) < 1e-6
+    g2, _ = O.density_grid(0.5, reset=False, grid=g1)
+    assert np.all(g2 <= g1) and np.all(g2 >= g1 * np.float32(0.5))
+    neg = sc.grid.copy(); neg[:100] = -1.0
+    g3, _ = O.density_grid(0.95, reset=False, grid=neg)
+    assert np.all(g3[:100] == -1.0)
+    # sigma itself: the floor of the EMA with decay 0 is 0.001691 * sigma(cell centre)
+    g4, _ = O.density_grid(0.0, reset=False, grid=np.zeros_like(sc.grid))
+    H = d.grid_size
+    idx = np.array([0, 5, H * H * 3 + H * 2 + 1, H ** 3 - 1])
+    ids = np.stack([idx // (H * H), idx % (H * H) // H, idx % H], 1).astype(np.float32)
+    centres = (np.float32(-1.0) + np.float32(2.0) / np.float32(H - 1) * ids) * np.float32(1.0 - 1.0 / H)
+    sig = O.samples((centres * np.float32(0.5) + np.float32(0.5)).astype(np.float32), np.full((4, 3), 0.5, np.float32))[:, 3]
+    assert np.allclose(g4[idx], np.float32(0.001691) * sig, rtol=1e-6)
+    gj, _ = O.density_grid(0.0, reset=False, seed=5, jitter=True, grid=np.zeros_like(sc.grid))
+    assert not np.array_equal(gj, g4)
