@@ -46,6 +46,18 @@ def peaks():
     return dict(hbm=6650.0, tf=1590.0, tf_sus=1400.0, src="fallback")
 
 
+def ncu_traffic(samples_per_launch):
+    """DRAM traffic of the dominant kernel per launch, from the committed ncu --set full capture of one full-size launch
+    (profiles/traffic_k_network.json, written by scripts/ncu_traffic.py): bytes per sample x this run's samples per launch."""
+    p = os.path.join(ROOT, "profiles", "traffic_k_network.json")
+    if not os.path.exists(p):
+        return {"traffic": None}
+    d = json.load(open(p))
+    return {"traffic": d["dram_bytes_per_sample"] * samples_per_launch,
+            "traffic_source": f"{d['dram_bytes_per_sample']:.1f} B/sample ({d['source']}, {d['workload']}) x samples per launch; "
+                              f"L1 wavefront pipe {d['l1_wavefronts_pct_of_peak']:.0f} % of peak, tensor pipe {d['tensor_pipe_pct']:.1f} % in that capture"}
+
+
 class ClockSampler:
     """nvidia-smi clocks during the timed region (B200_PROFILING.md clocks line)."""
 
@@ -250,7 +262,7 @@ def gpu_arm(args):
             "clocks": clocks,
             "roofline": {"kernel": "k_network<2> (hash-grid gather + tcgen05 MLP, fused)", "bound": "hbm",
                          "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s", "frac": achieved / pk["hbm"],
-                         "traffic": None, "peak_source": pk["src"] + " (HBM copy; the table is L2-resident, so >1 is possible)",
+                         **ncu_traffic(s_k), "peak_source": pk["src"] + " (HBM copy; the table is L2-resident, so >1 is possible)",
                          "algorithmic_bytes_per_sample": GATHER_BYTES_PER_SAMPLE + STREAM_BYTES_PER_SAMPLE,
                          "samples_per_launch": s_k, "ms_per_launch": net,
                          "mlp_tflops_in_fused": s_k * MLP_FLOP_PER_SAMPLE / (net * 1e-3) / 1e12,

@@ -63,26 +63,69 @@ struct Step {
 //                         itself (P.rbound = 1.0f/bound computed once on the host, IEEE)
 //   (n + .5 + .5*sign)/(H-1)   the numerator is the exact integer n or n+1, so the quotient comes from a table
 //                         lut[m] = (float)m / (float)(H-1) filled by the host's IEEE division (H+1 entries, shared memory)
-__device__ __forceinline__ bool march_step(const MarchParams& P, const float* __restrict__ lut, const float d[3],
-                                           const float rd[3], float& t, Step& s) {
-  const float x = clampf(P.o[0] + t * d[0], -P.bound, P.bound);
-  const float y = clampf(P.o[1] + t * d[1], -P.bound, P.bound);
-  const float z = clampf(P.o[2] + t * d[2], -P.bound, P.bound);
+//
+// FAST variant (P.fast: bound == 2^(C-1), H and 1/dt_gamma powers of two — every BASELINE config): the kernel is bound
+// by instruction issue (ncu: issue slots 80 % busy), so every step is trimmed WITHOUT changing a single rounding:
+//   * mip_bound is never capped, so it and its reciprocal are powers of two and products by them are exact;
+//     RN(a*p2 + c) is then one FFMA instead of FMUL+FADD (cell coordinate, cell-exit plane);
+//   * |x| <= mip_bound, so (x*rb+1)*H/2 >= 0 and the lower clamp of the cell coordinate is dead;
+//   * the position clamp to [-bound, bound] is the identity unless max|x_i| > bound (rounding at the box faces only):
+//     one compare on the max-norm the mip level needs anyway, the six FMNMX only in that rare case;
+//   * the table holds fl(2*lut[m] - 1) (same two roundings, done on the host) and is addressed from a per-ray base;
+//   * while dt_min <= t*dt_gamma <= dt_max the step t += clamp(t*dt_gamma) is RN(t + t*2^-k) = one FFMA.
+// The sample set depends on the whole chain of evaluated points (the reference's cell-exit planes use 1/(H-1) and do
+// not coincide with the cell faces, so a step may land one cell further), which rules out any hierarchical skipping:
+// the chain itself is reproduced, only cheaper.
+__device__ __forceinline__ float lds_f32(uint32_t saddr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(saddr));
+  return v;
+}
+
+struct RayCtx {
+  float d[3], rd[3];
+  uint32_t lut_a[3];  // shared-memory byte address of lut[1 - signbit(d_a)]: entry n + 1 (d >= +0) or n (sign set)
+};
+__device__ __forceinline__ void ray_ctx(const MarchParams& P, const float* lut, const float d[3], RayCtx& R) {
+  const uint32_t base = (uint32_t)__cvta_generic_to_shared(lut);
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    R.d[a] = d[a];
+    R.rd[a] = 1 / d[a];
+    // n + 0.5f + 0.5f*copysignf(1, d) is the integer n+1 (sign bit clear, incl. +0) or n (sign bit set, incl. -0)
+    R.lut_a[a] = base + 4u * (1u - (__float_as_uint(d[a]) >> 31));
+  }
+}
+
+template <bool FAST>
+__device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R, float& t, Step& s) {
+  float x = P.o[0] + t * R.d[0], y = P.o[1] + t * R.d[1], z = P.o[2] + t * R.d[2];
+  float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
+  if (!FAST || mx > P.bound) {
+    x = clampf(x, -P.bound, P.bound); y = clampf(y, -P.bound, P.bound); z = clampf(z, -P.bound, P.bound);
+    mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
+  }
   // mip_from_pos: frexpf exponent of the max-norm, clamped to [0, C-1]  (exact, done on the bit pattern)
-  const float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
   const int e = (int)((__float_as_uint(mx) >> 23) & 0xffu) - 126;
   const int level = max(0, min((int)P.C - 1, e));
   const float pow2 = __uint_as_float((uint32_t)(127 + level) << 23);
-  const bool capped = pow2 > P.bound;
+  const bool capped = !FAST && pow2 > P.bound;
   const float mip_bound = capped ? P.bound : pow2;
   const float mip_rbound = capped ? P.rbound : __uint_as_float((uint32_t)(127 - level) << 23);
   const uint32_t H = P.H;
   // reference: (int)clamp(0.5 /*double*/ * (x*rb+1) * H, 0, H-1).  0.5*H is exact in float and the double product is
   // exact, so one float multiply by (0.5f*H) rounds identically (DESIGN.md numerics contract).
   const float halfH = 0.5f * (float)H, hm1 = (float)(H - 1);
-  const int nx = (int)clampf((x * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
-  const int ny = (int)clampf((y * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
-  const int nz = (int)clampf((z * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
+  int nx, ny, nz;
+  if (FAST) {
+    nx = (int)fminf(__fmaf_rn(x, mip_rbound, 1.0f) * halfH, hm1);
+    ny = (int)fminf(__fmaf_rn(y, mip_rbound, 1.0f) * halfH, hm1);
+    nz = (int)fminf(__fmaf_rn(z, mip_rbound, 1.0f) * halfH, hm1);
+  } else {
+    nx = (int)clampf((x * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
+    ny = (int)clampf((y * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
+    nz = (int)clampf((z * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
+  }
   const uint32_t cell = ((level * H + nx) * H + ny) * H + nz;
   const bool occ = (__ldg(P.occupancy + (cell >> 5)) >> (cell & 31u)) & 1u;
   if (occ) {
@@ -94,42 +137,57 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const float* __
     s.level = level;
     return true;
   }
-  // n + 0.5f + 0.5f*copysignf(1, d) is the integer n+1 (sign bit clear, incl. +0) or n (sign bit set, incl. -0)
-  const float qx = lut[nx + 1 - (int)(__float_as_uint(d[0]) >> 31)];
-  const float qy = lut[ny + 1 - (int)(__float_as_uint(d[1]) >> 31)];
-  const float qz = lut[nz + 1 - (int)(__float_as_uint(d[2]) >> 31)];
-  const float tx = ((qx * 2.0f - 1.0f) * mip_bound - x) * rd[0];
-  const float ty = ((qy * 2.0f - 1.0f) * mip_bound - y) * rd[1];
-  const float tz = ((qz * 2.0f - 1.0f) * mip_bound - z) * rd[2];
+  const float qx = lds_f32(R.lut_a[0] + 4u * nx), qy = lds_f32(R.lut_a[1] + 4u * ny), qz = lds_f32(R.lut_a[2] + 4u * nz);
+  float tx, ty, tz;
+  if (FAST) {  // table entry = fl(2q - 1); (.)*mip_bound is exact, so RN((.)*mip_bound - x) is one FFMA
+    tx = __fmaf_rn(qx, mip_bound, -x) * R.rd[0];
+    ty = __fmaf_rn(qy, mip_bound, -y) * R.rd[1];
+    tz = __fmaf_rn(qz, mip_bound, -z) * R.rd[2];
+  } else {
+    tx = ((qx * 2.0f - 1.0f) * mip_bound - x) * R.rd[0];
+    ty = ((qy * 2.0f - 1.0f) * mip_bound - y) * R.rd[1];
+    tz = ((qz * 2.0f - 1.0f) * mip_bound - z) * R.rd[2];
+  }
   const float tt = t + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
-  do {
-    const float dt = clampf(t * P.dt_gamma, P.dt_min, P.dt_max);
-    t += dt;
-  } while (t < tt);
+  if (FAST && t >= P.t_lo && fmaxf(t, tt) <= P.t_hi) {
+    do { t = __fmaf_rn(t, P.dt_gamma, t); } while (t < tt);   // dt_min <= t*dt_gamma <= dt_max on every step taken
+  } else {
+    do {
+      const float dt = clampf(t * P.dt_gamma, P.dt_min, P.dt_max);
+      t += dt;
+    } while (t < tt);
+  }
   return false;
 }
 
+// lut (shared): FAST -> fl(2*m/(H-1) - 1), else m/(H-1); both tables sit back to back in P.div_lut
 __device__ __forceinline__ void load_lut(const MarchParams& P, float* lut) {
-  for (uint32_t i = threadIdx.x; i <= P.H; i += blockDim.x) lut[i] = __ldg(P.div_lut + i);
+  const float* src = P.div_lut + (P.fast ? P.H + 1 : 0);
+  for (uint32_t i = threadIdx.x; i <= P.H; i += blockDim.x) lut[i] = __ldg(src + i);
   __syncthreads();
 }
 
 // Whole-ray count; t_first = the t at which the first sample was taken (pass 2 restarts there: the march state is t)
-__device__ __forceinline__ int count_ray(const MarchParams& P, const float* lut, const float d[3], float near, float far,
-                                         float& t_first) {
-  const float rd[3] = {1 / d[0], 1 / d[1], 1 / d[2]};
+template <bool FAST>
+__device__ __forceinline__ int count_ray_t(const MarchParams& P, const RayCtx& R, float near, float far, float& t_first) {
   float t = near;
   int c = 0;
   t_first = near;
   Step s;
   while (t < far && c < NRF_MAX_STEPS_D) {
     const float t0 = t;
-    if (march_step(P, lut, d, rd, t, s)) {
+    if (march_step<FAST>(P, R, t, s)) {
       if (c == 0) t_first = t0;
       ++c;
     }
   }
   return c;
+}
+__device__ __forceinline__ int count_ray(const MarchParams& P, const float* lut, const float d[3], float near, float far,
+                                         float& t_first) {
+  RayCtx R;
+  ray_ctx(P, lut, d, R);
+  return P.fast ? count_ray_t<true>(P, R, near, far, t_first) : count_ray_t<false>(P, R, near, far, t_first);
 }
 
 // block-wide sum / exclusive scan helpers (128 threads, warp shuffles)
@@ -285,7 +343,8 @@ k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ 
   const uint32_t lt = (1u << lane) - 1u;
   const float4 r = rays[q];
   const float d[3] = {r.x, r.y, r.z};
-  const float rd[3] = {1 / d[0], 1 / d[1], 1 / d[2]};
+  RayCtx R;
+  ray_ctx(P, lut, d, R);
   const float2 ft = far_tf[q];
   const float far = ft.x;
   float t = ft.y;
@@ -293,8 +352,9 @@ k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ 
   long long off = base;
   const long long dbg0 = dbg ? dbg_offsets[q] : 0;
   Step s;
+  const bool fast = P.fast;
   while (t < far && c < c_total) {
-    if (!march_step(P, lut, d, rd, t, s)) continue;
+    if (!(fast ? march_step<true>(P, R, t, s) : march_step<false>(P, R, t, s))) continue;
     const long long k = off + __popc(alive & lt);
     samples[k] = make_float4(P.pos_w * s.x + 0.5f, P.pos_w * s.y + 0.5f, P.pos_w * s.z + 0.5f, s.dt);
     t_after[k] = t;

@@ -318,8 +318,13 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
   pack_weight(params + 5120, 64, 64, packed.data() + 5120);
   pack_weight(params + 9216, 16, 64, packed.data() + 9216);
   // division table of the march: lut[m] = (float)m / (float)(H-1), IEEE division on the host (kernels_exact.cu)
-  std::vector<float> lut(d.grid_size + 1);
-  for (uint32_t m = 0; m <= d.grid_size; ++m) lut[m] = (float)m / (float)(d.grid_size - 1);
+  // second half: fl(2*lut[m] - 1), the cell-exit plane in [-1,1] (render_utils.h:636-638), same two roundings
+  std::vector<float> lut(2 * (d.grid_size + 1));
+  for (uint32_t m = 0; m <= d.grid_size; ++m) {
+    const float q = (float)m / (float)(d.grid_size - 1);
+    lut[m] = q;
+    lut[d.grid_size + 1 + m] = q * 2.0f - 1.0f;
+  }
   CU(D.div_lut.ensure(lut.size()));
   CU(cudaMemcpyAsync(D.div_lut.p, lut.data(), lut.size() * sizeof(float), cudaMemcpyHostToDevice, D.stream));
   CU(D.mlp_packed.ensure(1280));
@@ -358,6 +363,14 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
   M.rbound = 1.0f / d.bound;
   M.occupancy = D.occupancy.p;
   M.div_lut = D.div_lut.p;
+  {
+    auto pow2f = [](float v) { int e; return v > 0 && std::frexp(v, &e) == 0.5f; };
+    const bool h_pow2 = (d.grid_size & (d.grid_size - 1)) == 0;
+    M.fast = (pow2f(M.dt_gamma) && h_pow2 && d.cascades <= 24 && d.bound == (float)(1u << (d.cascades - 1)) &&
+              !std::getenv("NRF_MARCH_GENERIC")) ? 1u : 0u;
+    M.t_lo = M.dt_min / M.dt_gamma;   // exact: dt_gamma is a power of two whenever `fast` is set
+    M.t_hi = M.dt_max / M.dt_gamma;
+  }
   return NRF_OK;
 }
 

@@ -51,7 +51,9 @@ struct MarchParams {
   int W;            // image width
   float rbound;     // 1/bound (IEEE, host)
   const uint32_t* occupancy;
-  const float* div_lut;  // div_lut[m] = (float)m / (float)(H-1), m = 0..H  (IEEE division done once on the host)
+  const float* div_lut;  // [0..H]: (float)m / (float)(H-1) (IEEE division done once on the host); [H+1..2H+1]: fl(2*that - 1)
+  uint32_t fast;         // bound == 2^(C-1), H and 1/dt_gamma powers of two: the trimmed march step (kernels_exact.cu)
+  float t_lo, t_hi;      // dt_min/dt_gamma, dt_max/dt_gamma: between them t*dt_gamma needs no clamp
 };
 
 // activation ids mirror include/nerf_b200.h

@@ -165,10 +165,13 @@ def make_scene(config="C2", seed=1337, rgb_activation=NRF_ACT_NONE, table_range=
     elif config == "tiny16":
         d = make_desc(14, 16.0, 5, rgb_activation)
         scene = "unbounded"
+    elif config == "tiny3":   # bound is not 2^(cascades-1): the outer cascade is capped at `bound` (generic march step)
+        d = make_desc(14, 3.0, 3, rgb_activation)
+        scene = "unbounded"
     else:
         raise ValueError(config)
     return Scene(d, random_params(d, seed, table_range), occupancy_grid(d, scene), aabb_of(d), config)
 
 
 def camera_radius(config: str) -> float:
-    return 12.0 if config in ("C3", "C4", "tiny16") else 4.0
+    return 12.0 if config in ("C3", "C4", "tiny16") else (7.0 if config == "tiny3" else 4.0)

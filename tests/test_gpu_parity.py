@@ -18,7 +18,7 @@ def bits(a):
     return np.ascontiguousarray(a, np.float32).view(np.uint32)
 
 
-@pytest.fixture(scope="module", params=["tiny", "tiny16"])
+@pytest.fixture(scope="module", params=["tiny", "tiny16", "tiny3"])
 def pair(request, built_lib):
     sc = syn.make_scene(request.param)
     r = NerfRender(1)
@@ -29,7 +29,10 @@ def pair(request, built_lib):
 
 
 def rel_err(a, b):
-    return np.abs(a - b) / np.maximum(np.abs(b), 1e-2)
+    """Relative error with an absolute floor: outputs are O(0.3); for |ref| < 0.02 (a sum of +- terms that cancels) the
+    error is the fp16 ulp of the hidden activations (~1e-4 absolute: the tensor core sums in another order than the
+    oracle's sequential fp32 loop, which the SIMT check kernel reproduces exactly), so it is measured against 0.02."""
+    return np.abs(a - b) / np.maximum(np.abs(b), 2e-2)
 
 
 def test_level_table_matches_oracle(pair):
