@@ -82,12 +82,24 @@ __device__ __forceinline__ float lds_f32(uint32_t saddr) {
   return v;
 }
 
+// The march loop is issue-bound and ptxas re-reads kernel parameters from the constant bank on every use (one LDC/LDCU
+// issue slot each, ~10 per step).  The per-frame constants the FAST step needs are therefore staged behind the table in
+// shared memory (load_lut) and read ONCE per ray with a volatile shared load, which pins them in vector registers.
+#define LUT_CONST 12  // o[3], bound, dt_gamma, halfH, hm1, t_lo, t_hi, H, C-1, (pad) behind the H+1 table entries
 struct RayCtx {
   float d[3], rd[3];
   uint32_t lut_a[3];  // shared-memory byte address of lut[1 - signbit(d_a)]: entry n + 1 (d >= +0) or n (sign set)
+  float o[3], bound, dt_gamma, halfH, hm1, t_lo, t_hi;   // pinned copies of per-frame constants
+  uint32_t H;
+  int cm1;
 };
 __device__ __forceinline__ void ray_ctx(const MarchParams& P, const float* lut, const float d[3], RayCtx& R) {
   const uint32_t base = (uint32_t)__cvta_generic_to_shared(lut);
+  const uint32_t cb = base + 4u * (P.H + 1);
+  R.o[0] = lds_f32(cb); R.o[1] = lds_f32(cb + 4); R.o[2] = lds_f32(cb + 8);
+  R.bound = lds_f32(cb + 12); R.dt_gamma = lds_f32(cb + 16); R.halfH = lds_f32(cb + 20); R.hm1 = lds_f32(cb + 24);
+  R.t_lo = lds_f32(cb + 28); R.t_hi = lds_f32(cb + 32);
+  R.H = __float_as_uint(lds_f32(cb + 36)); R.cm1 = (int)__float_as_uint(lds_f32(cb + 40));
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
     R.d[a] = d[a];
@@ -99,23 +111,23 @@ __device__ __forceinline__ void ray_ctx(const MarchParams& P, const float* lut, 
 
 template <bool FAST>
 __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R, float& t, Step& s) {
-  float x = P.o[0] + t * R.d[0], y = P.o[1] + t * R.d[1], z = P.o[2] + t * R.d[2];
+  float x = R.o[0] + t * R.d[0], y = R.o[1] + t * R.d[1], z = R.o[2] + t * R.d[2];
   float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
-  if (!FAST || mx > P.bound) {
-    x = clampf(x, -P.bound, P.bound); y = clampf(y, -P.bound, P.bound); z = clampf(z, -P.bound, P.bound);
+  if (!FAST || mx > R.bound) {
+    x = clampf(x, -R.bound, R.bound); y = clampf(y, -R.bound, R.bound); z = clampf(z, -R.bound, R.bound);
     mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
   }
   // mip_from_pos: frexpf exponent of the max-norm, clamped to [0, C-1]  (exact, done on the bit pattern)
   const int e = (int)((__float_as_uint(mx) >> 23) & 0xffu) - 126;
-  const int level = max(0, min((int)P.C - 1, e));
+  const int level = max(0, min(FAST ? R.cm1 : (int)P.C - 1, e));
   const float pow2 = __uint_as_float((uint32_t)(127 + level) << 23);
   const bool capped = !FAST && pow2 > P.bound;
   const float mip_bound = capped ? P.bound : pow2;
   const float mip_rbound = capped ? P.rbound : __uint_as_float((uint32_t)(127 - level) << 23);
-  const uint32_t H = P.H;
+  const uint32_t H = FAST ? R.H : P.H;
   // reference: (int)clamp(0.5 /*double*/ * (x*rb+1) * H, 0, H-1).  0.5*H is exact in float and the double product is
   // exact, so one float multiply by (0.5f*H) rounds identically (DESIGN.md numerics contract).
-  const float halfH = 0.5f * (float)H, hm1 = (float)(H - 1);
+  const float halfH = R.halfH, hm1 = R.hm1;
   int nx, ny, nz;
   if (FAST) {
     nx = (int)fminf(__fmaf_rn(x, mip_rbound, 1.0f) * halfH, hm1);
@@ -149,8 +161,8 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
     tz = ((qz * 2.0f - 1.0f) * mip_bound - z) * R.rd[2];
   }
   const float tt = t + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
-  if (FAST && t >= P.t_lo && fmaxf(t, tt) <= P.t_hi) {
-    do { t = __fmaf_rn(t, P.dt_gamma, t); } while (t < tt);   // dt_min <= t*dt_gamma <= dt_max on every step taken
+  if (FAST && t >= R.t_lo && fmaxf(t, tt) <= R.t_hi) {
+    do { t = __fmaf_rn(t, R.dt_gamma, t); } while (t < tt);   // dt_min <= t*dt_gamma <= dt_max on every step taken
   } else {
     do {
       const float dt = clampf(t * P.dt_gamma, P.dt_min, P.dt_max);
@@ -164,6 +176,12 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
 __device__ __forceinline__ void load_lut(const MarchParams& P, float* lut) {
   const float* src = P.div_lut + (P.fast ? P.H + 1 : 0);
   for (uint32_t i = threadIdx.x; i <= P.H; i += blockDim.x) lut[i] = __ldg(src + i);
+  if (threadIdx.x == 0) {
+    float* c = lut + P.H + 1;
+    c[0] = P.o[0]; c[1] = P.o[1]; c[2] = P.o[2]; c[3] = P.bound; c[4] = P.dt_gamma;
+    c[5] = 0.5f * (float)P.H; c[6] = (float)(P.H - 1); c[7] = P.t_lo; c[8] = P.t_hi;
+    c[9] = __uint_as_float(P.H); c[10] = __uint_as_float(P.C - 1u); c[11] = 0.f;
+  }
   __syncthreads();
 }
 
@@ -214,11 +232,11 @@ __device__ __forceinline__ void block_total(int c, int* __restrict__ block_sums)
 
 // Pass 1: rays of this shard (patch-major order, ShardMap) + sample counts + per-block totals.
 // rays: float4 {dx,dy,dz,near}; far_tf: float2 {far, t_first}; counts; block_sums[gridDim.x]
-extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, 8)
 k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, float4* __restrict__ rays,
              float2* __restrict__ far_tf, int* __restrict__ counts, int* __restrict__ block_sums,
              uint4* __restrict__ ray_sh) {
-  __shared__ float lut[NRF_MAX_GRID + 1];
+  __shared__ float lut[NRF_MAX_GRID + 1 + LUT_CONST];
   load_lut(P, lut);
   const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
   int c = 0;
@@ -257,10 +275,10 @@ k_rays_given_pixels(const __grid_constant__ MarchParams P, int pix0, int n, floa
 }
 
 // Count-only variant for externally supplied rays (stage probe nrf_probe_march).
-extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, 8)
 k_count_given(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays,
               float2* __restrict__ far_tf, int* __restrict__ counts, int* __restrict__ block_sums) {
-  __shared__ float lut[NRF_MAX_GRID + 1];
+  __shared__ float lut[NRF_MAX_GRID + 1 + LUT_CONST];
   load_lut(P, lut);
   const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
   int c = 0;
@@ -313,12 +331,12 @@ extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict
 // march in lockstep.  warp_base[] (first sample of every warp) is kept for the composite kernel.
 // samples: float4 {u,v,w,dt} (position already normalised: x*pos_w+0.5, nerf_render.cu:311-312), t_after, ray id.
 // dbg (optional, probe only): per sample {x,y,z,dt,t_after,level,cell,ray} raw, RAY-major at dbg_offsets[q] + k.
-extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, 8)
 k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays, const float2* __restrict__ far_tf,
        const int* __restrict__ counts, const int* __restrict__ block_bases, int* __restrict__ warp_base,
        float4* __restrict__ samples, float* __restrict__ t_after, int* __restrict__ sample_ray,
        float* __restrict__ dbg, const long long* __restrict__ dbg_offsets, long long capacity) {
-  __shared__ float lut[NRF_MAX_GRID + 1];
+  __shared__ float lut[NRF_MAX_GRID + 1 + LUT_CONST];
   __shared__ int wsum[RAYS_BLOCK / 32];
   __shared__ uint32_t died[RAYS_BLOCK / 32][NRF_MAX_STEPS_D];
   load_lut(P, lut);
