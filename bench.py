@@ -167,8 +167,21 @@ def gpu_arm(args):
     n_local = r.local_rays()
     ext = torch.cuda.ExternalStream(r.stream(), device=torch.device("cuda", local))
     rgb_ptr, dep_ptr, _ = r.device_outputs()
-    gatherer = local_rgb = host_frame = None
-    if world > 1:
+    gatherer = local_rgb = host_frame = fence = None
+    peer = world > 1 and args.gather == "peer"
+    if peer:
+        # the gather is fused into the composite kernel: rank 0 exports its frame buffer (CUDA IPC), every other rank
+        # maps it and stores its pixels there over NVLink; the only collective left is a 4-byte completion fence
+        handle = torch.zeros(64, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            handle.copy_(torch.frombuffer(bytearray(r.peer_frame_export()), dtype=torch.uint8))
+        dist.broadcast(handle, 0)
+        if rank != 0:
+            r.peer_frame_attach(bytes(handle.cpu().numpy().tobytes()))
+        with torch.cuda.stream(ext):
+            fence = torch.zeros(1, dtype=torch.int32, device="cuda")
+        dist.barrier()
+    elif world > 1:
         from nerf_cuda_b200.multigpu import FrameGather, FrameSharding
         sh = FrameSharding(W, H, world)
         with torch.cuda.stream(ext):
@@ -186,6 +199,15 @@ def gpu_arm(args):
                 r.render_frame_device(intr, pose)
                 return None
             r.render_frame_device(intr, pose)
+            if peer:
+                dist.all_reduce(fence)                      # completion fence (stream-ordered): every rank's stores landed
+                if to_host:
+                    if rank == 0:
+                        r.peer_frame_to_host()
+                    dist.all_reduce(fence)                  # nobody overwrites the frame before rank 0's copy is queued behind it
+                    if rank == 0:
+                        ext.synchronize()
+                return None
             full = gatherer(local_rgb)                      # NCCL gather of packed u8 tiles + tile transpose on rank 0
             if to_host and rank == 0:
                 host_frame.copy_(full, non_blocking=True)
@@ -252,12 +274,15 @@ def gpu_arm(args):
             "config": {"workload": f"{args.workload}: {W}x{H} frame, bound {sc.desc.bound:g}, {sc.desc.cascades} cascades, "
                                    f"log2_hashmap_size {sc.desc.log2_hashmap_size}, base.json MLPs, random-init weights, "
                                    f"synthetic occupancy, {len(poses)} orbit poses cycled",
-                       "sharding": "whole frame" if world == 1 else f"32x32-pixel tiles round-robin over {world} ranks, NCCL gather of packed u8 tiles to rank 0",
+                       "sharding": "whole frame" if world == 1 else (
+                           f"32x32-pixel tiles round-robin over {world} ranks; every rank's composite kernel stores its u8 pixels straight into "
+                           f"rank 0's frame over NVLink (CUDA IPC peer stores), 4-byte NCCL all-reduce as completion fence" if peer else
+                           f"32x32-pixel tiles round-robin over {world} ranks, NCCL gather of packed u8 tiles to rank 0"),
                        "samples_per_frame": smp_total, "samples_per_ray": smp_total / rays,
                        "l2": f"inputs larger than L2: each frame streams {smp_total / world * 60 / 1e6:.0f} MB of sample records per GPU "
                              f"and the pose changes every step; the {2 * int(syn.level_table(sc.desc)[0][-1]) * 2 / 1e6:.1f} MB hash table is L2-resident by design"},
             "e2e": {"value": rays * args.steps / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
-                    "h2d_bytes_per_step": 80, "d2h_bytes_per_step": rays * 4 + 8 if world == 1 else rays * 3 + 8},
+                    "h2d_bytes_per_step": 80, "d2h_bytes_per_step": rays * 4 + 8 if (world == 1 or peer) else rays * 3 + 8},
             "gpu_launches": 5 * args.steps,
             "clocks": clocks,
             "roofline": {"kernel": "k_network<2> (hash-grid gather + tcgen05 MLP, fused)", "bound": "hbm",
@@ -287,7 +312,13 @@ def gpu_arm(args):
         print(json.dumps(out), flush=True)
     # teardown order matters: every torch tensor that was used on the library's stream must be released (and the
     # caching allocator's blocks for that stream returned) BEFORE nrf_destroy destroys the stream
-    gatherer = local_rgb = host_frame = frame = timed = None
+    gatherer = local_rgb = host_frame = frame = timed = fence = None
+    if peer:
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank != 0:
+            r.peer_frame_detach()
+        dist.barrier()
     import gc
     gc.collect()
     torch.cuda.synchronize()
@@ -306,6 +337,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="N>1: peer = composite kernels store into rank 0's frame over NVLink (default); nccl = gather collective")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -29,6 +29,21 @@ int nrf_stream(nrf_ctx* ctx, void** stream);
  * q = local_tile*1024 + patch*32 + lane, patches of 8x4 pixels, 4x8 patches per tile). */
 int nrf_shard_pixel(nrf_ctx* ctx, int q, int* pixel);
 
+/* ---- peer frame: the gather fused into the composite kernel (one process per GPU) ---------------------------------
+ * The destination rank exports ONE frame buffer (rgb W*H*3 bytes followed by depth W*H bytes, pixel order) as a 64-byte
+ * CUDA IPC handle; every other rank attaches it.  From then on each rank's composite kernel stores its u8 pixels
+ * straight into that buffer over NVLink (peer stores), so no collective moves pixels: the caller only needs a
+ * completion fence (any stream-ordered collective, or a barrier after nrf_synchronize) before the destination reads.
+ * The exporting context writes into its own buffer directly.  Call after nrf_set_shard + nrf_set_resolution; detach
+ * before changing either.  (Reference: host threads + 2 D2H copies per GPU + CPU re-interleave, nerf_render.cu:345-358.) */
+int nrf_peer_frame_export(nrf_ctx* ctx, void* handle64);
+int nrf_peer_frame_attach(nrf_ctx* ctx, const void* handle64);
+int nrf_peer_frame_detach(nrf_ctx* ctx);
+/* Destination rank: device pointer of the frame; async copy to context-owned pinned memory on the context's stream
+ * (synchronise before reading *rgb / *depth, which stay valid until detach / destroy). */
+int nrf_peer_frame_device(nrf_ctx* ctx, void** frame);
+int nrf_peer_frame_to_host(nrf_ctx* ctx, uint8_t** rgb, uint8_t** depth);
+
 /* Memory micro-benchmarks on device 0 (roofline denominators for the hash gather).  mode 0: coalesced
  * 16-byte streaming reads over a window (window <= L2 size => L2->SM bandwidth, window >> L2 => HBM read bandwidth);
  * mode 1: one random 8-byte slot per lane (one 32-byte sector in its own 128-byte line: the access shape of a hashed

@@ -183,6 +183,31 @@ class NerfRender:
         _check(self._l.nrf_stream(self._ctx, C.byref(s)))
         return s.value or 0
 
+    # ---- peer frame (nerf_b200_ext.h): the gather fused into the composite kernel, one process per GPU ---------
+    def peer_frame_export(self) -> bytes:
+        h = (C.c_ubyte * 64)()
+        _check(self._l.nrf_peer_frame_export(self._ctx, h))
+        return bytes(h)
+
+    def peer_frame_attach(self, handle: bytes):
+        h = (C.c_ubyte * 64).from_buffer_copy(handle)
+        _check(self._l.nrf_peer_frame_attach(self._ctx, h))
+
+    def peer_frame_detach(self):
+        _check(self._l.nrf_peer_frame_detach(self._ctx))
+
+    def peer_frame_device(self) -> int:
+        p = C.c_void_p()
+        _check(self._l.nrf_peer_frame_device(self._ctx, C.byref(p)))
+        return p.value
+
+    def peer_frame_to_host(self):
+        """Async copy on the context's stream; returns (rgb[H,W,3], depth[H,W]) views — synchronize() before reading."""
+        rgb, dep = C.POINTER(C.c_ubyte)(), C.POINTER(C.c_ubyte)()
+        _check(self._l.nrf_peer_frame_to_host(self._ctx, C.byref(rgb), C.byref(dep)))
+        W, H = self.W, self.H
+        return (np.ctypeslib.as_array(rgb, shape=(H, W, 3)), np.ctypeslib.as_array(dep, shape=(H, W)))
+
     def bench_stage(self, what, n=0, iters=5) -> float:
         ms = C.c_float()
         _check(self._l.nrf_bench_stage(self._ctx, what, n, iters, C.byref(ms)))

@@ -11,6 +11,8 @@
 // __expf (ex2.approx) versus libm expf.
 #include "nrf_device.cuh"
 
+#define COMP_CHUNK 8
+
 extern "C" __global__ void __launch_bounds__(128)
 k_composite(int n_rays, ShardMap map, const int* __restrict__ warp_base, const int* __restrict__ counts,
             const float4* __restrict__ rays, const float2* __restrict__ far_tf, const float4* __restrict__ samples,
@@ -32,31 +34,50 @@ k_composite(int n_rays, ShardMap map, const int* __restrict__ warp_base, const i
   float tc = near, last_t = near;
   int used = 0;
   bool running = true;
-  for (int k = 0; k < cmax; ++k) {
-    const bool has = k < cnt;
-    const uint32_t alive = __ballot_sync(0xffffffffu, has);
-    if (has && running) {
-      const long long i = off + __popc(alive & lt);
-      const uint2 o = __ldg(sample_out + i);
-      const float dt = __ldg(samples + i).w;
-      const float ta = __ldg(t_after + i);
-      const __half2 rg = *reinterpret_cast<const __half2*>(&o.x);
-      const __half2 bs = *reinterpret_cast<const __half2*>(&o.y);
-      const float alpha = 1.0f - __expf(-__high2float(bs) * dt);
-      const float T = 1.0f - wsum;
-      const float w = alpha * T;
-      wsum += w;
-      tc += ta - last_t;   // deltas(1) = t - last_t (render_utils.h:629-631), accumulated like the reference
-      last_t = ta;
-      dep += w * tc;
-      cr += w * __low2float(rg);
-      cg += w * __high2float(rg);
-      cb += w * __low2float(bs);
-      ++used;
-      if ((double)T < 1e-4) running = false;   // the reference compares the float against a double literal
+  // The steps of a ray are sequential, but WHERE its samples live is not data-dependent (ballot/popc of the counts), so
+  // the loop runs in chunks of COMP_CHUNK steps: all indices first, then all loads in flight at once, then the
+  // sequential accumulation.  Without this the kernel's critical path is one DRAM latency per step of its longest ray
+  // (1024 steps = 0.28 ms), which is what one frame shard took on 8 GPUs.
+  for (int k0 = 0; k0 < cmax; k0 += COMP_CHUNK) {
+    long long idx[COMP_CHUNK];
+    bool has[COMP_CHUNK];
+#pragma unroll
+    for (int j = 0; j < COMP_CHUNK; ++j) {
+      has[j] = k0 + j < cnt;
+      const uint32_t alive = __ballot_sync(0xffffffffu, has[j]);
+      idx[j] = off + __popc(alive & lt);
+      off += __popc(alive);
     }
-    off += __popc(alive);
-    if (!__any_sync(0xffffffffu, has && running)) break;
+    uint2 so[COMP_CHUNK];
+    float dts[COMP_CHUNK], tas[COMP_CHUNK];
+#pragma unroll
+    for (int j = 0; j < COMP_CHUNK; ++j) {
+      if (has[j] && running) {
+        so[j] = __ldg(sample_out + idx[j]);
+        dts[j] = __ldg(&samples[idx[j]].w);
+        tas[j] = __ldg(t_after + idx[j]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < COMP_CHUNK; ++j) {
+      if (has[j] && running) {
+        const __half2 rg = *reinterpret_cast<const __half2*>(&so[j].x);
+        const __half2 bs = *reinterpret_cast<const __half2*>(&so[j].y);
+        const float alpha = 1.0f - __expf(-__high2float(bs) * dts[j]);
+        const float T = 1.0f - wsum;
+        const float w = alpha * T;
+        wsum += w;
+        tc += tas[j] - last_t;   // deltas(1) = t - last_t (render_utils.h:629-631), accumulated like the reference
+        last_t = tas[j];
+        dep += w * tc;
+        cr += w * __low2float(rg);
+        cg += w * __high2float(rg);
+        cb += w * __low2float(bs);
+        ++used;
+        if ((double)T < 1e-4) running = false;   // the reference compares the float against a double literal
+      }
+    }
+    if (!__any_sync(0xffffffffu, running && k0 + COMP_CHUNK < cnt)) break;
   }
   const float bg = 1.0f;  // m_bg_color, nerf_render.h:74
   const float R = cr + (1.0f - wsum) * bg, G = cg + (1.0f - wsum) * bg, B = cb + (1.0f - wsum) * bg;

@@ -227,6 +227,11 @@ struct nrf_ctx {
   bool loaded = false;
   int W = 0, H = 0;
   int shard = 0, n_shards = 1;    // process-level sharding (one process per GPU); requires a single-device context
+  // peer frame of the one-process-per-GPU mode: ONE W*H*4-byte buffer (rgb W*H*3 | depth W*H) owned by the destination
+  // rank and mapped into every other rank through CUDA IPC; composites store their pixels straight into it over NVLink
+  uint8_t* peer_frame = nullptr;  // device pointer valid in THIS process (own allocation or IPC mapping)
+  bool peer_owned = false, peer_mapped = false;
+  uint8_t* peer_host = nullptr;   // pinned W*H*4, destination rank only
   uint8_t* rgb_host = nullptr;    // pinned, W*H*3 (full frame when n_shards == 1, else this shard's packed tiles)
   uint8_t* depth_host = nullptr;  // pinned, W*H
   nrf_stats stats{};
@@ -284,6 +289,13 @@ static void free_device(Device& D) {
 
 extern "C" int nrf_destroy(nrf_ctx* c) {
   if (!c) return NRF_OK;
+  if (c->peer_frame) {
+    cudaSetDevice(c->devs[0].dev);
+    cudaStreamSynchronize(c->devs[0].stream);
+    if (c->peer_mapped) cudaIpcCloseMemHandle(c->peer_frame);
+    else if (c->peer_owned) cudaFree(c->peer_frame);
+  }
+  if (c->peer_host) cudaFreeHost(c->peer_host);
   for (Device& D : c->devs) free_device(D);
   if (c->rgb_host) cudaFreeHost(c->rgb_host);
   if (c->depth_host) cudaFreeHost(c->depth_host);
@@ -459,6 +471,7 @@ extern "C" int nrf_set_shard(nrf_ctx* c, int shard, int n_shards) {
   if (!c || n_shards < 1 || shard < 0 || shard >= n_shards) return fail(NRF_EINVAL, "nrf_set_shard: bad arguments");
   if (n_shards > 1 && c->devs.size() != 1)
     return fail(NRF_EINVAL, "process-level sharding needs a single-device context (one process per GPU)");
+  if (c->peer_frame) return fail(NRF_ESTATE, "nrf_set_shard: detach the peer frame first");
   c->shard = shard;
   c->n_shards = n_shards;
   c->W = c->H = 0;  // force re-allocation on the next set_resolution
@@ -471,6 +484,8 @@ extern "C" int nrf_set_resolution(nrf_ctx* c, int W, int H) {
   if (!c->loaded) return fail(NRF_ESTATE, "set_resolution must follow reload_network_from_file");  // nerf_render.cu:226
   if ((long long)W * H > (1ll << 29)) return fail(NRF_EINVAL, "resolution too large");
   if (c->W == W && c->H == H) return NRF_OK;
+  if (c->peer_frame) return fail(NRF_ESTATE, "nrf_set_resolution: detach the peer frame before changing the resolution");
+  if (c->peer_host) { cudaFreeHost(c->peer_host); c->peer_host = nullptr; }
   const int n_dev = (int)c->devs.size();
   const int total_shards = c->n_shards * n_dev;
   // Several devices in one process write their pixels straight into device 0's frame over NVLink (peer stores)
@@ -617,7 +632,9 @@ static int frame_phase_b(nrf_ctx* c, Device& D) {
     Device& D0 = c->devs[0];
     k_composite<<<nb, 128, 0, D.stream>>>(D.n_local, D.map, D.warp_base.p, D.counts.p, D.rays.p, D.far_tf.p, D.samples.p,
                                           D.t_after.p, D.sample_out.p, D.rgb_f32.p, D.depth_f32.p, D.used.p,
-                                          D0.rgb_u8.p, D0.depth_u8.p, c->n_shards == 1 ? 1 : 0);
+                                          c->peer_frame ? c->peer_frame : D0.rgb_u8.p,
+                                          c->peer_frame ? c->peer_frame + (size_t)c->W * c->H * 3 : D0.depth_u8.p,
+                                          (c->n_shards == 1 || c->peer_frame) ? 1 : 0);
     CU(cudaGetLastError());
   }
   CU(cudaEventRecord(D.ev[4], D.stream));
@@ -1108,5 +1125,83 @@ extern "C" int nrf_postprocess(nrf_ctx* c, int n_pixels, const float* frame_rgba
   }
   CU(cudaStreamSynchronize(D.stream));
   f.release(); a.release(); o.release();
+  return NRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- peer frame (IPC)
+// One process per GPU: instead of gathering packed tiles with a collective after the frame, every rank's composite
+// kernel stores its u8 pixels straight into ONE frame buffer that lives on the destination rank's GPU (NVLink peer
+// stores through a CUDA-IPC mapping) — the compute step and the gather are the same kernel, exactly like the
+// one-process n-GPU mode.  The caller orders "all ranks finished" -> "destination reads" with one stream-ordered
+// collective of 4 bytes (bench.py) or a barrier.
+static int peer_detach(nrf_ctx* c) {
+  if (!c->peer_frame) return NRF_OK;
+  CU(cudaSetDevice(c->devs[0].dev));
+  CU(cudaStreamSynchronize(c->devs[0].stream));
+  if (c->peer_mapped) CU(cudaIpcCloseMemHandle(c->peer_frame));
+  else if (c->peer_owned) CU(cudaFree(c->peer_frame));
+  c->peer_frame = nullptr;
+  c->peer_owned = c->peer_mapped = false;
+  return NRF_OK;
+}
+
+extern "C" int nrf_peer_frame_export(nrf_ctx* c, void* handle64) {
+  if (!c || !handle64) return fail(NRF_EINVAL, "nrf_peer_frame_export: null argument");
+  if (!c->W) return fail(NRF_ESTATE, "set_resolution not called");
+  if (c->devs.size() != 1) return fail(NRF_EINVAL, "peer frame needs a single-device context (one process per GPU)");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  int rc = peer_detach(c);
+  if (rc) return rc;
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  const size_t bytes = (size_t)c->W * c->H * 4;
+  CU(cudaMalloc(&c->peer_frame, bytes));
+  c->peer_owned = true;
+  CU(cudaMemsetAsync(c->peer_frame, 0, bytes, D.stream));
+  CU(cudaStreamSynchronize(D.stream));
+  if (!c->peer_host) CU(cudaMallocHost(&c->peer_host, bytes));
+  cudaIpcMemHandle_t h;
+  CU(cudaIpcGetMemHandle(&h, c->peer_frame));
+  std::memcpy(handle64, &h, 64);
+  return NRF_OK;
+}
+
+extern "C" int nrf_peer_frame_attach(nrf_ctx* c, const void* handle64) {
+  if (!c || !handle64) return fail(NRF_EINVAL, "nrf_peer_frame_attach: null argument");
+  if (!c->W) return fail(NRF_ESTATE, "set_resolution not called");
+  if (c->devs.size() != 1) return fail(NRF_EINVAL, "peer frame needs a single-device context (one process per GPU)");
+  int rc = peer_detach(c);
+  if (rc) return rc;
+  CU(cudaSetDevice(c->devs[0].dev));
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle64, 64);
+  void* p = nullptr;
+  CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  c->peer_frame = (uint8_t*)p;
+  c->peer_mapped = true;
+  return NRF_OK;
+}
+
+extern "C" int nrf_peer_frame_detach(nrf_ctx* c) {
+  if (!c) return fail(NRF_EINVAL, "null ctx");
+  return peer_detach(c);
+}
+
+// Destination rank: device pointer of the frame (rgb W*H*3 | depth W*H), and an async copy of it to pinned host memory
+// on the context's stream (call after the completion fence; synchronise the stream before reading *rgb / *depth).
+extern "C" int nrf_peer_frame_device(nrf_ctx* c, void** frame) {
+  if (!c || !frame) return fail(NRF_EINVAL, "null argument");
+  if (!c->peer_frame) return fail(NRF_ESTATE, "no peer frame");
+  *frame = c->peer_frame;
+  return NRF_OK;
+}
+extern "C" int nrf_peer_frame_to_host(nrf_ctx* c, uint8_t** rgb, uint8_t** depth) {
+  if (!c) return fail(NRF_EINVAL, "null ctx");
+  if (!c->peer_frame || !c->peer_owned) return fail(NRF_ESTATE, "not the owner of a peer frame");
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  CU(cudaMemcpyAsync(c->peer_host, c->peer_frame, (size_t)c->W * c->H * 4, cudaMemcpyDeviceToHost, D.stream));
+  if (rgb) *rgb = c->peer_host;
+  if (depth) *depth = c->peer_host + (size_t)c->W * c->H * 3;
   return NRF_OK;
 }

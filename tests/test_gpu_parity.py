@@ -1,6 +1,8 @@
 """Parity tests proper (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle on the same seeded
 inputs.  Bars (BASELINE.json north_star): rays / traversal / sample counts / hash indices / fp16 features BIT-EXACT;
 per-sample sigma and rgb within 1e-2 relative (fp16 MLP); images max abs <= 2/255 and PSNR >= 45 dB."""
+import os
+
 import numpy as np
 import pytest
 
@@ -333,3 +335,56 @@ def test_postprocess_accumulate_and_tonemap(pair, color_space, out_space, curve)
     _, out_g2 = r.postprocess(acc_o, None, 0.0, color_space, -1.0, bg, out_space, curve, False)
     assert np.all(np.abs(out_g2 - out_o2) <= 2e-6 + 4e-6 * np.abs(out_o2))
     assert r.postprocess(np.zeros((0, 4), np.float32), None)[1].shape == (0, 4)
+
+
+_PEER_CHILD = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1])
+from nerf_cuda_b200 import NerfRender, synthetic as syn
+name, W, H, shard, world, az = sys.argv[2], int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5]), int(sys.argv[6]), float(sys.argv[7])
+sc = syn.make_scene(name)
+r = NerfRender(1)
+r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+r.set_shard(shard, world)
+r.set_resolution((W, H))
+r.peer_frame_attach(bytes.fromhex(sys.stdin.readline().strip()))
+r.render_frame_device(syn.intrinsics(W, H), syn.look_at_pose(syn.camera_radius(name), 20.0, az))
+r.synchronize()
+r.peer_frame_detach()
+r.close()
+print("child done")
+"""
+
+
+def test_peer_frame_ipc_two_processes(pair, tmp_path):
+    """One process per GPU with the gather fused into the composite kernel: the destination rank exports its frame
+    buffer through CUDA IPC, another PROCESS attaches it and its composite stores its tiles straight into that buffer.
+    (Both processes share the one GPU here; on a multi-GPU box the same stores cross NVLink.)  The assembled frame must
+    equal the unsharded frame byte for byte."""
+    import subprocess, sys as _sys
+    name, sc, r, O = pair
+    W, H, world, az = 150, 90, 2, 140.0
+    intr, pose = syn.intrinsics(W, H), syn.look_at_pose(syn.camera_radius(name), 20.0, az)
+    r.set_shard(0, 1)
+    r.set_resolution((W, H))
+    full_rgb, full_dep = (a.copy() for a in r.render_frame(intr, pose))
+    r0 = NerfRender(1)
+    r0.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    r0.set_shard(0, world)
+    r0.set_resolution((W, H))
+    handle = r0.peer_frame_export()
+    script = tmp_path / "peer_child.py"
+    script.write_text(_PEER_CHILD)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    child = subprocess.Popen([_sys.executable, str(script), root, name, str(W), str(H), "1", str(world), str(az)],
+                             stdin=subprocess.PIPE, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    out, err = child.communicate(handle.hex() + "\n", timeout=300)
+    assert child.returncode == 0 and "child done" in out, err[-2000:]
+    r0.render_frame_device(intr, pose)          # this rank's tiles, stored into its own buffer
+    rgb, dep = r0.peer_frame_to_host()
+    r0.synchronize()
+    assert np.array_equal(rgb, full_rgb) and np.array_equal(dep, full_dep)
+    with pytest.raises(Exception):
+        r0.set_resolution((W + 1, H))           # must detach first
+    r0.peer_frame_detach()
+    r0.close()
