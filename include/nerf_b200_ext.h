@@ -35,7 +35,9 @@ int nrf_shard_pixel(nrf_ctx* ctx, int q, int* pixel);
  * straight into that buffer over NVLink (peer stores), so no collective moves pixels: the caller only needs a
  * completion fence (any stream-ordered collective, or a barrier after nrf_synchronize) before the destination reads.
  * The exporting context writes into its own buffer directly.  Call after nrf_set_shard + nrf_set_resolution; detach
- * before changing either.  (Reference: host threads + 2 D2H copies per GPU + CPU re-interleave, nerf_render.cu:345-358.) */
+ * before changing either.  A frame whose samples do not fit the context's buffers is re-rendered at that rank's next
+ * host sync point (nrf_synchronize, ...): either synchronise every rank before the fence, or — as bench.py does — size
+ * the buffers with one untimed pass over the poses first, after which a stream-ordered fence alone is enough.  (Reference: host threads + 2 D2H copies per GPU + CPU re-interleave, nerf_render.cu:345-358.) */
 int nrf_peer_frame_export(nrf_ctx* ctx, void* handle64);
 int nrf_peer_frame_attach(nrf_ctx* ctx, const void* handle64);
 int nrf_peer_frame_detach(nrf_ctx* ctx);

@@ -22,14 +22,15 @@ k_composite(int n_rays, ShardMap map, const int* __restrict__ warp_base, const i
   const int lane = threadIdx.x & 31;
   const int q = blockIdx.x * blockDim.x + threadIdx.x;   // n_rays is a multiple of 32: whole warps only
   if (q >= n_rays) return;
-  const int cnt = counts[q];
+  const int wb = warp_base[q >> 5];
+  const int cnt = wb < 0 ? 0 : counts[q];   // wb < 0: the patch did not fit the sample buffers (frame will be redone)
   const float4 ray = rays[q];
   const float near = ray.w, far = far_tf[q].x;
   int cmax = cnt;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, o));
   const uint32_t lt = (1u << lane) - 1u;
-  long long off = warp_base[q >> 5];
+  long long off = wb;
   float wsum = 0.f, dep = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
   float tc = near, last_t = near;
   int used = 0;

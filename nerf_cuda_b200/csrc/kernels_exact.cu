@@ -355,9 +355,12 @@ k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ 
   __syncthreads();
   long long base = block_bases[blockIdx.x];
   for (int w = 0; w < warp; ++w) base += wsum[w];
-  if (lane == 0 && q < n) warp_base[q >> 5] = (int)base;
+  // a patch whose samples do not fit the buffers is skipped and marked (warp_base = -1: k_composite skips it too); the
+  // host sees total > capacity at the end of the frame, grows the buffers and renders the frame again
+  const bool overflow = base + wsum[warp] > capacity;
+  if (lane == 0 && q < n) warp_base[q >> 5] = overflow ? -1 : (int)base;
   uint32_t alive = __ballot_sync(0xffffffffu, c_total > 0);
-  if (c_total == 0 || base + wsum[warp] > capacity) return;
+  if (c_total == 0 || overflow) return;
   const uint32_t lt = (1u << lane) - 1u;
   const float4 r = rays[q];
   const float d[3] = {r.x, r.y, r.z};

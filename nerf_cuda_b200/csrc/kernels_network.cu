@@ -280,7 +280,16 @@ template <int MODE>
 __global__ void __launch_bounds__(NET_THREADS, 1)
 k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__ samples,
           const int* __restrict__ sample_ray, const float4* __restrict__ rays, const uint4* __restrict__ ray_sh,
-          int dirs_mode, uint4* __restrict__ enc_io, uint2* __restrict__ out, uint32_t* __restrict__ idx_out) {
+          int dirs_mode, uint4* __restrict__ enc_io, uint2* __restrict__ out, uint32_t* __restrict__ idx_out,
+          const unsigned long long* __restrict__ n_dev) {
+  // frame path: the sample count is still in device memory when this kernel is enqueued (no host round trip in the
+  // middle of a frame); `n` is then the capacity of the sample buffers
+  // (a total above the capacity means the list has holes — k_emit skipped the patches that did not fit — and the host
+  // will render the frame again with larger buffers: nothing to do here)
+  if (n_dev) {
+    const unsigned long long total = __ldg(n_dev);
+    n = total > (unsigned long long)n ? 0 : (int)total;
+  }
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* sW = smem;
   uint64_t* mbars = reinterpret_cast<uint64_t*>(smem + SMEM_W_BYTES);           // one per group
@@ -534,13 +543,13 @@ static void nrf_network_setup() {
 extern "C" cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t stream, const NetParams* P, int n,
                                           const float4* samples, const int* sample_ray, const float4* rays,
                                           const uint4* ray_sh, int dirs_mode, uint4* enc_io, uint2* out,
-                                          uint32_t* idx_out) {
+                                          uint32_t* idx_out, const unsigned long long* n_dev) {
   nrf_network_setup();
   if (n <= 0) return cudaSuccess;
   switch (mode) {
-    case 0: k_network<0><<<grid, NET_THREADS, NET_SMEM, stream>>>(*P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out); break;
-    case 1: k_network<1><<<grid, NET_THREADS, NET_SMEM, stream>>>(*P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out); break;
-    default: k_network<2><<<grid, NET_THREADS, NET_SMEM, stream>>>(*P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out); break;
+    case 0: k_network<0><<<grid, NET_THREADS, NET_SMEM, stream>>>(*P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out, n_dev); break;
+    case 1: k_network<1><<<grid, NET_THREADS, NET_SMEM, stream>>>(*P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out, n_dev); break;
+    default: k_network<2><<<grid, NET_THREADS, NET_SMEM, stream>>>(*P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out, n_dev); break;
   }
   return cudaGetLastError();
 }

@@ -52,7 +52,8 @@ __global__ void k_composite(int n_rays, ShardMap map, const int* warp_base, cons
 size_t nrf_network_smem_bytes();
 cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t stream, const NetParams* P, int n,
                                const float4* samples, const int* sample_ray, const float4* rays, const uint4* ray_sh,
-                               int dirs_mode, uint4* enc_io, uint2* out, uint32_t* idx_out);
+                               int dirs_mode, uint4* enc_io, uint2* out, uint32_t* idx_out,
+                               const unsigned long long* n_dev);
 cudaError_t nrf_launch_encode_exp(int variant, int sms, cudaStream_t stream, const NetParams* P, int n,
                                   const float4* samples, uint4* enc_io);
 cudaError_t nrf_launch_network_simt(cudaStream_t stream, const NetParams* P, int n, const uint4* enc,
@@ -235,6 +236,9 @@ struct nrf_ctx {
   uint8_t* rgb_host = nullptr;    // pinned, W*H*3 (full frame when n_shards == 1, else this shard's packed tiles)
   uint8_t* depth_host = nullptr;  // pinned, W*H
   nrf_stats stats{};
+  // a frame that was enqueued without a host sync (its sample total is still unchecked against the buffer capacity)
+  bool pending = false, pending_to_host = false;
+  float pending_intr[4] = {}, pending_pose[16] = {};
 };
 
 static int device_count() {
@@ -242,6 +246,9 @@ static int device_count() {
   if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
   return n;
 }
+
+struct nrf_ctx;
+static int frame_resolve(nrf_ctx* c);  // host sync point of an asynchronously enqueued frame (defined with the frame code)
 
 extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
   if (!out || n_gpus < 1) return fail(NRF_EINVAL, "nrf_create: bad arguments");
@@ -289,6 +296,8 @@ static void free_device(Device& D) {
 
 extern "C" int nrf_destroy(nrf_ctx* c) {
   if (!c) return NRF_OK;
+  c->pending = false;
+  for (Device& D : c->devs) { cudaSetDevice(D.dev); if (D.stream) cudaStreamSynchronize(D.stream); }
   if (c->peer_frame) {
     cudaSetDevice(c->devs[0].dev);
     cudaStreamSynchronize(c->devs[0].stream);
@@ -389,6 +398,7 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
 extern "C" int nrf_load_raw(nrf_ctx* c, const nrf_model_desc* desc, const float* params, size_t n_params,
                             const float* density_grid, size_t n_grid, const float aabb[6]) {
   if (!c || !desc || !params || !density_grid || !aabb) return fail(NRF_EINVAL, "nrf_load_raw: null argument");
+  { int rc_ = frame_resolve(c); if (rc_) return rc_; }
   int rc = check_arch(*desc);
   if (rc) return rc;
   HostLevels lv;
@@ -469,6 +479,7 @@ extern "C" int nrf_get_model_desc(nrf_ctx* c, nrf_model_desc* out) {
 // ---------------------------------------------------------------------------------------------------- resolution
 extern "C" int nrf_set_shard(nrf_ctx* c, int shard, int n_shards) {
   if (!c || n_shards < 1 || shard < 0 || shard >= n_shards) return fail(NRF_EINVAL, "nrf_set_shard: bad arguments");
+  { int rc_ = frame_resolve(c); if (rc_) return rc_; }
   if (n_shards > 1 && c->devs.size() != 1)
     return fail(NRF_EINVAL, "process-level sharding needs a single-device context (one process per GPU)");
   if (c->peer_frame) return fail(NRF_ESTATE, "nrf_set_shard: detach the peer frame first");
@@ -483,6 +494,7 @@ extern "C" int nrf_set_resolution(nrf_ctx* c, int W, int H) {
   if (!c || W < 1 || H < 1) return fail(NRF_EINVAL, "nrf_set_resolution: bad arguments");
   if (!c->loaded) return fail(NRF_ESTATE, "set_resolution must follow reload_network_from_file");  // nerf_render.cu:226
   if ((long long)W * H > (1ll << 29)) return fail(NRF_EINVAL, "resolution too large");
+  { int rc = frame_resolve(c); if (rc) return rc; }
   if (c->W == W && c->H == H) return NRF_OK;
   if (c->peer_frame) return fail(NRF_ESTATE, "nrf_set_resolution: detach the peer frame before changing the resolution");
   if (c->peer_host) { cudaFreeHost(c->peer_host); c->peer_host = nullptr; }
@@ -560,6 +572,7 @@ extern "C" int nrf_stream(nrf_ctx* c, void** stream) {
 
 extern "C" int nrf_synchronize(nrf_ctx* c) {
   if (!c) return fail(NRF_EINVAL, "null ctx");
+  { int rc = frame_resolve(c); if (rc) return rc; }
   for (Device& D : c->devs) {
     CU(cudaSetDevice(D.dev));
     CU(cudaStreamSynchronize(D.stream));
@@ -587,11 +600,19 @@ static int network_grid(nrf_ctx*, const Device& D, int n_samples) {
   return std::max(1, std::min(D.n_sms, (tiles + 7) / 8));
 }
 
-// Phase A (async): rays + count + scan, then the 8-byte total read-back.
-static int frame_phase_a(nrf_ctx* c, Device& D, const float intr[4], const float* pose) {
+// One frame on one device, enqueued WITHOUT a host round trip: rays + count + scan leave the sample total in device
+// memory, k_emit / k_network / k_composite read it there; the sample buffers keep the capacity of earlier frames.
+// If the total exceeds the capacity the overflowing patches are skipped on the device (k_emit marks them) and
+// frame_check() — at the next host sync — grows the buffers and asks for the frame to be rendered again.
+static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float* pose) {
   CU(cudaSetDevice(D.dev));
   set_pose(c, D.march, intr, pose);
   const int nb = (D.n_local + 127) / 128;
+  if (D.samples.n == 0) {  // first frame at this resolution: start from 32 samples per ray
+    const size_t want = std::max<size_t>((size_t)D.n_local * 32, 4096);
+    CU(D.samples.ensure(want)); CU(D.t_after.ensure(want)); CU(D.sample_ray.ensure(want)); CU(D.sample_out.ensure(want));
+  }
+  const size_t cap = std::min<size_t>(D.samples.n, (1ull << 31) - 256);
   CU(cudaEventRecord(D.ev[0], D.stream));
   if (D.n_local > 0) {
     k_rays_count<<<nb, 128, 0, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
@@ -602,31 +623,15 @@ static int frame_phase_a(nrf_ctx* c, Device& D, const float intr[4], const float
   CU(cudaGetLastError());
   CU(cudaEventRecord(D.ev[1], D.stream));
   CU(cudaMemcpyAsync(D.total_h, D.total.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, D.stream));
-  return NRF_OK;
-}
-
-// Phase B: emit + network + composite; the u8 pixels land in device 0's frame (peer stores from the other devices).
-static int frame_phase_b(nrf_ctx* c, Device& D) {
-  CU(cudaSetDevice(D.dev));
-  CU(cudaStreamSynchronize(D.stream));
-  const unsigned long long S = D.total_h[0];
-  if (S > (1ull << 31) - 256) return fail(NRF_EINVAL, "frame produces %llu samples (> 2^31)", S);
-  D.last_samples = S;
-  const size_t cap = std::max<size_t>((size_t)S, 1);
-  if (cap > D.samples.n) {
-    const size_t want = cap + cap / 4;
-    CU(D.samples.ensure(want)); CU(D.t_after.ensure(want)); CU(D.sample_ray.ensure(want)); CU(D.sample_out.ensure(want));
-  }
-  const int nb = (D.n_local + 127) / 128;
   if (D.n_local > 0) {
     k_emit<<<nb, 128, 0, D.stream>>>(D.march, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
                                     D.warp_base.p, D.samples.p, D.t_after.p, D.sample_ray.p, nullptr, nullptr,
-                                    (long long)D.samples.n);
+                                    (long long)cap);
     CU(cudaGetLastError());
   }
   CU(cudaEventRecord(D.ev[2], D.stream));
-  CU(nrf_launch_network(2, network_grid(c, D, (int)S), D.stream, &D.net, (int)S, D.samples.p, D.sample_ray.p, D.rays.p,
-                        D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr));
+  CU(nrf_launch_network(2, network_grid(c, D, (int)cap), D.stream, &D.net, (int)cap, D.samples.p, D.sample_ray.p, D.rays.p,
+                        D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr, D.total.p));
   CU(cudaEventRecord(D.ev[3], D.stream));
   if (D.n_local > 0) {
     Device& D0 = c->devs[0];
@@ -639,6 +644,20 @@ static int frame_phase_b(nrf_ctx* c, Device& D) {
   }
   CU(cudaEventRecord(D.ev[4], D.stream));
   CU(cudaEventRecord(D.done, D.stream));
+  return NRF_OK;
+}
+
+// After the device's stream has been synchronised: 1 = the frame overflowed the sample buffers (now grown), render again.
+static int frame_check(nrf_ctx*, Device& D, bool& redo) {
+  CU(cudaSetDevice(D.dev));
+  const unsigned long long S = D.total_h[0];
+  if (S > (1ull << 31) - 256) return fail(NRF_EINVAL, "frame produces %llu samples (> 2^31)", S);
+  D.last_samples = S;
+  if (S > D.samples.n) {
+    const size_t want = (size_t)S + (size_t)S / 4;
+    CU(D.samples.ensure(want)); CU(D.t_after.ensure(want)); CU(D.sample_ray.ensure(want)); CU(D.sample_out.ensure(want));
+    redo = true;
+  }
   return NRF_OK;
 }
 
@@ -656,18 +675,47 @@ static int frame_to_host(nrf_ctx* c) {
   return NRF_OK;
 }
 
+static int frame_enqueue_all(nrf_ctx* c, const float intr[4], const float* pose, bool to_host) {
+  for (Device& D : c->devs) { int rc = frame_enqueue(c, D, intr, pose); if (rc) return rc; }
+  if (to_host) return frame_to_host(c);
+  CU(cudaSetDevice(c->devs[0].dev));
+  CU(cudaEventRecord(c->devs[0].ev[5], c->devs[0].stream));
+  return NRF_OK;
+}
+
+// Host sync point: wait for the enqueued frame, validate its sample total, re-render if the buffers were too small
+// (at most twice: the exact total is known after the first attempt).
+static int frame_resolve(nrf_ctx* c) {
+  if (!c->pending) return NRF_OK;
+  for (int attempt = 0; attempt < 3; ++attempt) {
+    bool redo = false;
+    for (Device& D : c->devs) {
+      CU(cudaSetDevice(D.dev));
+      CU(cudaStreamSynchronize(D.stream));
+      int rc = frame_check(c, D, redo);
+      if (rc) { c->pending = false; return rc; }
+    }
+    if (!redo) { c->pending = false; return NRF_OK; }
+    int rc = frame_enqueue_all(c, c->pending_intr, c->pending_pose, c->pending_to_host);
+    if (rc) { c->pending = false; return rc; }
+  }
+  c->pending = false;
+  return fail(NRF_ECUDA, "frame did not fit its sample buffers after regrowing them");
+}
+
 static int render_common(nrf_ctx* c, const float intr[4], const float* pose, bool to_host, bool sync) {
   if (!c || !intr || !pose) return fail(NRF_EINVAL, "render: null argument");
   if (!c->loaded) return fail(NRF_ESTATE, "render_frame before reload_network_from_file");
   if (!c->W) return fail(NRF_ESTATE, "render_frame before set_resolution");
-  for (Device& D : c->devs) { int rc = frame_phase_a(c, D, intr, pose); if (rc) return rc; }
-  for (Device& D : c->devs) { int rc = frame_phase_b(c, D); if (rc) return rc; }
-  if (to_host) { int rc = frame_to_host(c); if (rc) return rc; }
-  else { CU(cudaSetDevice(c->devs[0].dev)); CU(cudaEventRecord(c->devs[0].ev[5], c->devs[0].stream)); }
-  if (sync) {
-    for (Device& D : c->devs) { CU(cudaSetDevice(D.dev)); CU(cudaStreamSynchronize(D.stream)); }
-  }
-  return NRF_OK;
+  int rc = frame_resolve(c);   // an earlier asynchronous frame must be validated before its buffers are reused
+  if (rc) return rc;
+  rc = frame_enqueue_all(c, intr, pose, to_host);
+  if (rc) return rc;
+  c->pending = true;
+  c->pending_to_host = to_host;
+  std::memcpy(c->pending_intr, intr, 16);
+  std::memcpy(c->pending_pose, pose, 64);
+  return sync ? frame_resolve(c) : NRF_OK;
 }
 
 extern "C" int nrf_render_frame(nrf_ctx* c, const float intr[4], const float pose[16], uint8_t** rgb, uint8_t** depth) {
@@ -698,6 +746,7 @@ extern "C" int nrf_render_batch(nrf_ctx* c, const float intr[4], const float* po
 
 extern "C" int nrf_get_float_frame(nrf_ctx* c, float* rgb_f32, float* depth_f32, int32_t* samples_per_ray) {
   if (!c || !c->W) return fail(NRF_ESTATE, "no frame rendered");
+  { int rc = frame_resolve(c); if (rc) return rc; }
   // gathers in GLOBAL pixel order when the context covers the whole frame, else in local order
   const bool whole = c->n_shards == 1;
   size_t off = 0;
@@ -729,6 +778,7 @@ extern "C" int nrf_get_float_frame(nrf_ctx* c, float* rgb_f32, float* depth_f32,
 extern "C" int nrf_get_stats(nrf_ctx* c, nrf_stats* out) {
   if (!c || !out) return fail(NRF_EINVAL, "null argument");
   if (!c->W) return fail(NRF_ESTATE, "no frame rendered");
+  { int rc = frame_resolve(c); if (rc) return rc; }
   nrf_stats s{};
   s.n_rays = (uint64_t)c->W * c->H;
   s.n_gpus = (uint32_t)c->devs.size();
@@ -866,7 +916,7 @@ extern "C" int nrf_probe_encode(nrf_ctx* c, int n, const float* positions, uint1
   CU(D.enc.ensure((size_t)n * 4));
   if (indices_out) CU(D.idx.ensure((size_t)n * NRF_L * 8));
   CU(nrf_launch_network(0, network_grid(c, D, n), D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p,
-                        nullptr, indices_out ? D.idx.p : nullptr));
+                        nullptr, indices_out ? D.idx.p : nullptr, nullptr));
   CU(cudaMemcpyAsync(enc_out, D.enc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, D.stream));
   if (indices_out) CU(cudaMemcpyAsync(indices_out, D.idx.p, (size_t)n * NRF_L * 8 * 4, cudaMemcpyDeviceToHost, D.stream));
   CU(cudaStreamSynchronize(D.stream));
@@ -885,7 +935,7 @@ extern "C" int nrf_probe_network(nrf_ctx* c, int n, const uint16_t* enc, const f
   CU(D.enc.ensure((size_t)n * 4)); CU(o.ensure(n));
   CU(cudaMemcpyAsync(D.enc.p, enc, (size_t)n * 64, cudaMemcpyHostToDevice, D.stream));
   if (impl == 1) CU(nrf_launch_network_simt(D.stream, &D.net, n, D.enc.p, d4.p, o.p));
-  else CU(nrf_launch_network(1, network_grid(c, D, n), D.stream, &D.net, n, nullptr, nullptr, d4.p, nullptr, 1, D.enc.p, o.p, nullptr));
+  else CU(nrf_launch_network(1, network_grid(c, D, n), D.stream, &D.net, n, nullptr, nullptr, d4.p, nullptr, 1, D.enc.p, o.p, nullptr, nullptr));
   std::vector<uint2> h(n);
   CU(cudaMemcpyAsync(h.data(), o.p, (size_t)n * 8, cudaMemcpyDeviceToHost, D.stream));
   CU(cudaStreamSynchronize(D.stream));
@@ -904,7 +954,7 @@ extern "C" int nrf_probe_samples(nrf_ctx* c, int n, const float* positions, cons
   if (!rc) rc = upload_vec3_as_float4(D, n, dirs, d4);
   if (rc) return rc;
   CU(o.ensure(n));
-  CU(nrf_launch_network(2, network_grid(c, D, n), D.stream, &D.net, n, p4.p, nullptr, d4.p, nullptr, 1, nullptr, o.p, nullptr));
+  CU(nrf_launch_network(2, network_grid(c, D, n), D.stream, &D.net, n, p4.p, nullptr, d4.p, nullptr, 1, nullptr, o.p, nullptr, nullptr));
   std::vector<uint2> h(n);
   CU(cudaMemcpyAsync(h.data(), o.p, (size_t)n * 8, cudaMemcpyDeviceToHost, D.stream));
   CU(cudaStreamSynchronize(D.stream));
@@ -919,6 +969,7 @@ extern "C" int nrf_probe_samples(nrf_ctx* c, int n, const float* positions, cons
 // stream; between iterations nothing else touches L2 than the stage itself (the sample stream is >> L2 at full size).
 extern "C" int nrf_bench_stage(nrf_ctx* c, int what, int n, int iters, float* ms_out) {
   NEED_MODEL(c);
+  { int rc_ = frame_resolve(c); if (rc_) return rc_; }
   if (!ms_out || iters < 1 || what < 0 || what > 2) return fail(NRF_EINVAL, "nrf_bench_stage: bad arguments");
   Device& D = c->devs[0];
   CU(cudaSetDevice(D.dev));
@@ -927,13 +978,13 @@ extern "C" int nrf_bench_stage(nrf_ctx* c, int what, int n, int iters, float* ms
   CU(D.enc.ensure((size_t)S * 4));
   const int grid = network_grid(c, D, S);
   if (what == 1)  // produce the features once
-    CU(nrf_launch_network(0, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, nullptr, nullptr));
+    CU(nrf_launch_network(0, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, nullptr, nullptr, nullptr));
   cudaEvent_t e0, e1;
   CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
-  CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, D.sample_out.p, nullptr));
+  CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, D.sample_out.p, nullptr, nullptr));
   CU(cudaEventRecord(e0, D.stream));
   for (int i = 0; i < iters; ++i)
-    CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, D.sample_out.p, nullptr));
+    CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, D.sample_out.p, nullptr, nullptr));
   CU(cudaEventRecord(e1, D.stream));
   CU(cudaEventSynchronize(e1));
   float ms = 0;
@@ -955,10 +1006,10 @@ extern "C" int nrf_bench_encode_positions(nrf_ctx* c, int n, const float* positi
   const int grid = network_grid(c, D, n);
   cudaEvent_t e0, e1;
   CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
-  CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr));
+  CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr, nullptr));
   CU(cudaEventRecord(e0, D.stream));
   for (int i = 0; i < iters; ++i)
-    CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr));
+    CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr, nullptr));
   CU(cudaEventRecord(e1, D.stream));
   CU(cudaEventSynchronize(e1));
   float ms = 0;
@@ -971,6 +1022,7 @@ extern "C" int nrf_bench_encode_positions(nrf_ctx* c, int n, const float* positi
 // Experiment hook (not in the public header): encode-only occupancy variants on the last frame's samples.
 extern "C" int nrf_exp_encode(nrf_ctx* c, int variant, int iters, float* ms_out) {
   NEED_MODEL(c);
+  { int rc_ = frame_resolve(c); if (rc_) return rc_; }
   Device& D = c->devs[0];
   CU(cudaSetDevice(D.dev));
   const int S = (int)D.last_samples;
@@ -1036,6 +1088,7 @@ extern "C" int nrf_bench_memory(nrf_ctx* c, int mode, size_t window_bytes, int i
 extern "C" int nrf_generate_density_grid(nrf_ctx* c, float decay, int reset, unsigned long long jitter_seed, int jitter,
                                          float* mean_density_out) {
   NEED_MODEL(c);
+  { int rc_ = frame_resolve(c); if (rc_) return rc_; }
   const nrf_model_desc& d = c->desc;
   const uint32_t H = d.grid_size, H3 = H * H * H;
   float mean = 0.f;
@@ -1056,7 +1109,7 @@ extern "C" int nrf_generate_density_grid(nrf_ctx* c, float decay, int reset, uns
                                                            3ull * cas * H3, D.samples.p);
       CU(cudaGetLastError());
       CU(nrf_launch_network(2, network_grid(c, D, (int)H3), D.stream, &D.net, (int)H3, D.samples.p, D.sample_ray.p,
-                            D.rays.p, D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr));
+                            D.rays.p, D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr, nullptr));
       k_dg_update<<<(H3 + 255) / 256, 256, 0, D.stream>>>(H3, D.sample_out.p, decay, reset,
                                                         D.density_grid.p + (size_t)cas * H3, sum.p);
       CU(cudaGetLastError());
@@ -1147,6 +1200,7 @@ static int peer_detach(nrf_ctx* c) {
 
 extern "C" int nrf_peer_frame_export(nrf_ctx* c, void* handle64) {
   if (!c || !handle64) return fail(NRF_EINVAL, "nrf_peer_frame_export: null argument");
+  { int rc_ = frame_resolve(c); if (rc_) return rc_; }
   if (!c->W) return fail(NRF_ESTATE, "set_resolution not called");
   if (c->devs.size() != 1) return fail(NRF_EINVAL, "peer frame needs a single-device context (one process per GPU)");
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
@@ -1168,6 +1222,7 @@ extern "C" int nrf_peer_frame_export(nrf_ctx* c, void* handle64) {
 
 extern "C" int nrf_peer_frame_attach(nrf_ctx* c, const void* handle64) {
   if (!c || !handle64) return fail(NRF_EINVAL, "nrf_peer_frame_attach: null argument");
+  { int rc_ = frame_resolve(c); if (rc_) return rc_; }
   if (!c->W) return fail(NRF_ESTATE, "set_resolution not called");
   if (c->devs.size() != 1) return fail(NRF_EINVAL, "peer frame needs a single-device context (one process per GPU)");
   int rc = peer_detach(c);
@@ -1184,6 +1239,7 @@ extern "C" int nrf_peer_frame_attach(nrf_ctx* c, const void* handle64) {
 
 extern "C" int nrf_peer_frame_detach(nrf_ctx* c) {
   if (!c) return fail(NRF_EINVAL, "null ctx");
+  { int rc_ = frame_resolve(c); if (rc_) return rc_; }
   return peer_detach(c);
 }
 
@@ -1198,6 +1254,7 @@ extern "C" int nrf_peer_frame_device(nrf_ctx* c, void** frame) {
 extern "C" int nrf_peer_frame_to_host(nrf_ctx* c, uint8_t** rgb, uint8_t** depth) {
   if (!c) return fail(NRF_EINVAL, "null ctx");
   if (!c->peer_frame || !c->peer_owned) return fail(NRF_ESTATE, "not the owner of a peer frame");
+  { int rc_ = frame_resolve(c); if (rc_) return rc_; }   // this rank's own frame must be valid before it is copied
   Device& D = c->devs[0];
   CU(cudaSetDevice(D.dev));
   CU(cudaMemcpyAsync(c->peer_host, c->peer_frame, (size_t)c->W * c->H * 4, cudaMemcpyDeviceToHost, D.stream));

@@ -388,3 +388,33 @@ def test_peer_frame_ipc_two_processes(pair, tmp_path):
         r0.set_resolution((W + 1, H))           # must detach first
     r0.peer_frame_detach()
     r0.close()
+
+
+def test_async_frames_and_buffer_regrowth(pair):
+    """Frames are enqueued without a host round trip (the sample total stays on the device); a frame that does not fit
+    the sample buffers is detected at the next sync point, the buffers grow and the frame is rendered again.  A fresh
+    context starts at 32 samples per ray, so its first frames exercise exactly that; results must equal the synchronous
+    path bit for bit."""
+    name, sc, r, O = pair
+    W, H = 64, 48
+    intr = syn.intrinsics(W, H)
+    pa, pb = (syn.look_at_pose(syn.camera_radius(name), 20.0, az) for az in (15.0, 200.0))
+    r.set_shard(0, 1)
+    r.set_resolution((W, H))
+    ref = {}
+    for key, p in (("a", pa), ("b", pb)):
+        u8 = r.render_frame(intr, p)[0].copy()
+        ref[key] = (u8,) + tuple(x.copy() for x in r.float_frame()) + (r.stats().n_samples,)
+    r2 = NerfRender(1)
+    r2.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    r2.set_resolution((W, H))
+    r2.render_frame_device(intr, pa)          # overflows the initial buffers (pending, unchecked)
+    r2.render_frame_device(intr, pb)          # resolves frame a (regrow + redo), then enqueues b
+    fb = r2.float_frame()                     # sync point: validates b
+    assert all(np.array_equal(x, y) for x, y in zip(fb, ref["b"][1:4])) and r2.stats().n_samples == ref["b"][4]
+    r2.render_frame_device(intr, pa)
+    r2.synchronize()
+    fa = r2.float_frame()
+    assert all(np.array_equal(x, y) for x, y in zip(fa, ref["a"][1:4])) and r2.stats().n_samples == ref["a"][4]
+    assert np.array_equal(r2.render_frame(intr, pb)[0], ref["b"][0])
+    r2.close()
