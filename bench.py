@@ -201,12 +201,9 @@ def gpu_arm(args):
             r.render_frame_device(intr, pose)
             if peer:
                 dist.all_reduce(fence)                      # completion fence (stream-ordered): every rank's stores landed
-                if to_host:
-                    if rank == 0:
-                        r.peer_frame_to_host()
-                    dist.all_reduce(fence)                  # nobody overwrites the frame before rank 0's copy is queued behind it
-                    if rank == 0:
-                        ext.synchronize()
+                if to_host and rank == 0:                   # the peer frame is double-buffered: the next frame's stores go
+                    r.peer_frame_to_host()                  # to the other half, and ITS fence orders this copy before the
+                    ext.synchronize()                       # half is written again — one collective per frame
                 return None
             full = gatherer(local_rgb)                      # NCCL gather of packed u8 tiles + tile transpose on rank 0
             if to_host and rank == 0:

@@ -30,8 +30,10 @@ int nrf_stream(nrf_ctx* ctx, void** stream);
 int nrf_shard_pixel(nrf_ctx* ctx, int q, int* pixel);
 
 /* ---- peer frame: the gather fused into the composite kernel (one process per GPU) ---------------------------------
- * The destination rank exports ONE frame buffer (rgb W*H*3 bytes followed by depth W*H bytes, pixel order) as a 64-byte
- * CUDA IPC handle; every other rank attaches it.  From then on each rank's composite kernel stores its u8 pixels
+ * The destination rank exports ONE buffer holding two frames used alternately (each: rgb W*H*3 bytes followed by depth
+ * W*H bytes, pixel order) as a 64-byte CUDA IPC handle; every other rank attaches it.  Frames alternate so that the
+ * destination may still be copying frame i out while the others store frame i+1: with one fence per frame, the fence of
+ * frame i+1 orders the end of that copy before anyone stores frame i+2.  Every rank must render every frame.  From then on each rank's composite kernel stores its u8 pixels
  * straight into that buffer over NVLink (peer stores), so no collective moves pixels: the caller only needs a
  * completion fence (any stream-ordered collective, or a barrier after nrf_synchronize) before the destination reads.
  * The exporting context writes into its own buffer directly.  Call after nrf_set_shard + nrf_set_resolution; detach

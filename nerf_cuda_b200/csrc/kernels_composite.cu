@@ -89,15 +89,39 @@ k_composite(int n_rays, ShardMap map, const int* __restrict__ warp_base, const i
   used_counts[q] = used;
   // (unsigned char)(255.0 * v): double multiply + truncation (nerf_render.cu:355-358); clamped where that is UB (D4)
   int px, py;
-  if (!shard_pixel_xy(map, q, px, py)) return;
-  const long long dst = u8_pixel_order ? (long long)py * map.W + px : shard_packed_index(q);
+  const bool inside = shard_pixel_xy(map, q, px, py);
   const float v4[4] = {R, G, B, D};
-  uint8_t u[4];
+  uint32_t u[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     const double x = 255.0 * (double)v4[k];
-    u[k] = !(x >= 0.0) ? 0 : (x >= 255.0 ? 255 : (uint8_t)(int)x);
+    u[k] = !(x >= 0.0) ? 0u : (x >= 255.0 ? 255u : (uint32_t)(int)x);
   }
-  rgb_u8[dst * 3 + 0] = u[0]; rgb_u8[dst * 3 + 1] = u[1]; rgb_u8[dst * 3 + 2] = u[2];
-  depth_u8[dst] = u[3];
+  // Word-packed stores.  A patch row is 8 consecutive pixels = 24 rgb bytes + 8 depth bytes, 4-byte aligned whenever the
+  // row stride is (always in the packed tile layout; in pixel order when W % 4 == 0): lanes 0-5 of the row store the six
+  // rgb words, lanes 6-7 the two depth words, the bytes collected with warp shuffles.  32 bytes per row in 8 stores
+  // instead of 32 single-byte stores — these stores cross NVLink when the frame lives on another GPU.
+  const int col = lane & 7, row0 = lane & 24;
+  const uint32_t rgb24 = inside ? (u[0] | (u[1] << 8) | (u[2] << 16)) : 0u;
+  const uint32_t dep8 = inside ? u[3] : 0u;
+  const int c6 = min(col, 5), p0 = (4 * c6) / 3;                      // first pixel contributing to rgb word c6
+  const uint32_t lo = __shfl_sync(0xffffffffu, rgb24, row0 + p0), hi = __shfl_sync(0xffffffffu, rgb24, row0 + min(p0 + 1, 7));
+  const uint32_t rgb_word = (uint32_t)((((unsigned long long)hi << 24) | lo) >> (8 * (4 * c6 - 3 * p0)));
+  const int d4 = (col & 1) * 4;
+  uint32_t dep_word = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) dep_word |= __shfl_sync(0xffffffffu, dep8, row0 + d4 + k) << (8 * k);
+  // the row's first pixel decides: whole row inside the image (or packed layout, where outside slots exist and hold 0)
+  const int px0 = __shfl_sync(0xffffffffu, px, row0), py0 = __shfl_sync(0xffffffffu, py, row0);
+  const bool row_inside = px0 + 8 <= map.W && py0 < map.H;
+  const bool vec = u8_pixel_order ? (row_inside && (map.W & 3) == 0) : true;
+  if (vec) {
+    const long long base = u8_pixel_order ? (long long)py0 * map.W + px0 : (long long)shard_packed_index(q - col);
+    if (col < 6) reinterpret_cast<uint32_t*>(rgb_u8 + base * 3)[col] = rgb_word;
+    else reinterpret_cast<uint32_t*>(depth_u8 + base)[col - 6] = dep_word;
+  } else if (inside) {
+    const long long dst = (long long)py * map.W + px;
+    rgb_u8[dst * 3 + 0] = (uint8_t)u[0]; rgb_u8[dst * 3 + 1] = (uint8_t)u[1]; rgb_u8[dst * 3 + 2] = (uint8_t)u[2];
+    depth_u8[dst] = (uint8_t)u[3];
+  }
 }

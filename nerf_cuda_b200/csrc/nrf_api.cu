@@ -232,6 +232,7 @@ struct nrf_ctx {
   // rank and mapped into every other rank through CUDA IPC; composites store their pixels straight into it over NVLink
   uint8_t* peer_frame = nullptr;  // device pointer valid in THIS process (own allocation or IPC mapping)
   bool peer_owned = false, peer_mapped = false;
+  int peer_slot = 0;              // the buffer holds TWO frames used alternately (see nrf_peer_frame_export)
   uint8_t* peer_host = nullptr;   // pinned W*H*4, destination rank only
   uint8_t* rgb_host = nullptr;    // pinned, W*H*3 (full frame when n_shards == 1, else this shard's packed tiles)
   uint8_t* depth_host = nullptr;  // pinned, W*H
@@ -600,6 +601,8 @@ static int network_grid(nrf_ctx*, const Device& D, int n_samples) {
   return std::max(1, std::min(D.n_sms, (tiles + 7) / 8));
 }
 
+static inline uint8_t* peer_slot_ptr(nrf_ctx* c) { return c->peer_frame + (size_t)c->peer_slot * c->W * c->H * 4; }
+
 // One frame on one device, enqueued WITHOUT a host round trip: rays + count + scan leave the sample total in device
 // memory, k_emit / k_network / k_composite read it there; the sample buffers keep the capacity of earlier frames.
 // If the total exceeds the capacity the overflowing patches are skipped on the device (k_emit marks them) and
@@ -637,8 +640,8 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
     Device& D0 = c->devs[0];
     k_composite<<<nb, 128, 0, D.stream>>>(D.n_local, D.map, D.warp_base.p, D.counts.p, D.rays.p, D.far_tf.p, D.samples.p,
                                           D.t_after.p, D.sample_out.p, D.rgb_f32.p, D.depth_f32.p, D.used.p,
-                                          c->peer_frame ? c->peer_frame : D0.rgb_u8.p,
-                                          c->peer_frame ? c->peer_frame + (size_t)c->W * c->H * 3 : D0.depth_u8.p,
+                                          c->peer_frame ? peer_slot_ptr(c) : D0.rgb_u8.p,
+                                          c->peer_frame ? peer_slot_ptr(c) + (size_t)c->W * c->H * 3 : D0.depth_u8.p,
                                           (c->n_shards == 1 || c->peer_frame) ? 1 : 0);
     CU(cudaGetLastError());
   }
@@ -709,6 +712,7 @@ static int render_common(nrf_ctx* c, const float intr[4], const float* pose, boo
   if (!c->W) return fail(NRF_ESTATE, "render_frame before set_resolution");
   int rc = frame_resolve(c);   // an earlier asynchronous frame must be validated before its buffers are reused
   if (rc) return rc;
+  c->peer_slot ^= 1;           // every rank renders every frame, so all ranks alternate in step
   rc = frame_enqueue_all(c, intr, pose, to_host);
   if (rc) return rc;
   c->pending = true;
@@ -1208,12 +1212,15 @@ extern "C" int nrf_peer_frame_export(nrf_ctx* c, void* handle64) {
   if (rc) return rc;
   Device& D = c->devs[0];
   CU(cudaSetDevice(D.dev));
-  const size_t bytes = (size_t)c->W * c->H * 4;
+  // TWO frames, written alternately: the destination can still be copying frame i out while the other ranks store
+  // frame i+1 — the completion fence of frame i+1 then orders "copy of i finished" before anyone stores frame i+2
+  const size_t bytes = (size_t)c->W * c->H * 4 * 2;
+  c->peer_slot = 0;
   CU(cudaMalloc(&c->peer_frame, bytes));
   c->peer_owned = true;
   CU(cudaMemsetAsync(c->peer_frame, 0, bytes, D.stream));
   CU(cudaStreamSynchronize(D.stream));
-  if (!c->peer_host) CU(cudaMallocHost(&c->peer_host, bytes));
+  if (!c->peer_host) CU(cudaMallocHost(&c->peer_host, bytes / 2));
   cudaIpcMemHandle_t h;
   CU(cudaIpcGetMemHandle(&h, c->peer_frame));
   std::memcpy(handle64, &h, 64);
@@ -1234,6 +1241,7 @@ extern "C" int nrf_peer_frame_attach(nrf_ctx* c, const void* handle64) {
   CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
   c->peer_frame = (uint8_t*)p;
   c->peer_mapped = true;
+  c->peer_slot = 0;
   return NRF_OK;
 }
 
@@ -1248,7 +1256,7 @@ extern "C" int nrf_peer_frame_detach(nrf_ctx* c) {
 extern "C" int nrf_peer_frame_device(nrf_ctx* c, void** frame) {
   if (!c || !frame) return fail(NRF_EINVAL, "null argument");
   if (!c->peer_frame) return fail(NRF_ESTATE, "no peer frame");
-  *frame = c->peer_frame;
+  *frame = peer_slot_ptr(c);
   return NRF_OK;
 }
 extern "C" int nrf_peer_frame_to_host(nrf_ctx* c, uint8_t** rgb, uint8_t** depth) {
@@ -1257,7 +1265,7 @@ extern "C" int nrf_peer_frame_to_host(nrf_ctx* c, uint8_t** rgb, uint8_t** depth
   { int rc_ = frame_resolve(c); if (rc_) return rc_; }   // this rank's own frame must be valid before it is copied
   Device& D = c->devs[0];
   CU(cudaSetDevice(D.dev));
-  CU(cudaMemcpyAsync(c->peer_host, c->peer_frame, (size_t)c->W * c->H * 4, cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaMemcpyAsync(c->peer_host, peer_slot_ptr(c), (size_t)c->W * c->H * 4, cudaMemcpyDeviceToHost, D.stream));
   if (rgb) *rgb = c->peer_host;
   if (depth) *depth = c->peer_host + (size_t)c->W * c->H * 3;
   return NRF_OK;

@@ -2,7 +2,7 @@
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -6
-for g in peer nccl; do
+for g in peer; do
 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29531 bench.py --gpus 2 --steps 16 --warmup 4 --gather $g > gpurun_out/scale2_$g.json 2> gpurun_out/scale2_$g.err; echo "$g rc=$?"
 python -c "
 import json
