@@ -218,6 +218,7 @@ struct Device {
   DevBuf<uint32_t> idx;
   DevBuf<float> dbg;
   unsigned long long last_samples = 0;
+  unsigned frame_no = 0;          // frames enqueued; the total of frame f lands in total_h[f & 3]
 };
 
 struct nrf_ctx {
@@ -266,6 +267,7 @@ extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
     for (int k = 0; k < 6 && e == cudaSuccess; ++k) e = cudaEventCreate(&D.ev[k]);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&D.done, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaMallocHost(&D.total_h, 4 * sizeof(unsigned long long));
+    if (e == cudaSuccess) std::memset(D.total_h, 0, 4 * sizeof(unsigned long long));
     cudaDeviceProp prop;
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, D.dev);
     if (e != cudaSuccess) {
@@ -625,7 +627,8 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
   k_scan_blocks<<<1, 1024, 0, D.stream>>>(D.block_sums.p, D.n_local > 0 ? nb : 0, D.total.p);
   CU(cudaGetLastError());
   CU(cudaEventRecord(D.ev[1], D.stream));
-  CU(cudaMemcpyAsync(D.total_h, D.total.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, D.stream));
+  ++D.frame_no;
+  CU(cudaMemcpyAsync(D.total_h + (D.frame_no & 3u), D.total.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, D.stream));
   if (D.n_local > 0) {
     k_emit<<<nb, 128, 0, D.stream>>>(D.march, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
                                     D.warp_base.p, D.samples.p, D.t_after.p, D.sample_ray.p, nullptr, nullptr,
@@ -650,17 +653,24 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
   return NRF_OK;
 }
 
-// After the device's stream has been synchronised: 1 = the frame overflowed the sample buffers (now grown), render again.
+// After the device's stream has been synchronised: validates the LATEST frame's sample total (redo = it overflowed the
+// buffers and must be rendered again) and grows the buffers to the largest total any recent frame reported (frames
+// may be enqueued back to back without a host sync; only the latest one's result is still observable, the older
+// totals — a ring of four — are growth hints).
 static int frame_check(nrf_ctx*, Device& D, bool& redo) {
   CU(cudaSetDevice(D.dev));
-  const unsigned long long S = D.total_h[0];
-  if (S > (1ull << 31) - 256) return fail(NRF_EINVAL, "frame produces %llu samples (> 2^31)", S);
+  const unsigned long long S = D.total_h[D.frame_no & 3u];
+  unsigned long long mx = 0;
+  for (int k = 0; k < 4; ++k) { mx = std::max(mx, D.total_h[k]); D.total_h[k] = 0; }
+  D.total_h[D.frame_no & 3u] = S;
+  if (mx > (1ull << 31) - 256) return fail(NRF_EINVAL, "frame produces %llu samples (> 2^31)", mx);
   D.last_samples = S;
-  if (S > D.samples.n) {
-    const size_t want = (size_t)S + (size_t)S / 4;
+  const size_t cap = D.samples.n;
+  if (mx > cap) {
+    const size_t want = (size_t)mx + (size_t)mx / 4;
     CU(D.samples.ensure(want)); CU(D.t_after.ensure(want)); CU(D.sample_ray.ensure(want)); CU(D.sample_out.ensure(want));
-    redo = true;
   }
+  if (S > cap) redo = true;
   return NRF_OK;
 }
 
@@ -710,8 +720,9 @@ static int render_common(nrf_ctx* c, const float intr[4], const float* pose, boo
   if (!c || !intr || !pose) return fail(NRF_EINVAL, "render: null argument");
   if (!c->loaded) return fail(NRF_ESTATE, "render_frame before reload_network_from_file");
   if (!c->W) return fail(NRF_ESTATE, "render_frame before set_resolution");
-  int rc = frame_resolve(c);   // an earlier asynchronous frame must be validated before its buffers are reused
-  if (rc) return rc;
+  // No host sync here: an earlier asynchronous frame that is still unvalidated is superseded (its buffers are reused
+  // in stream order; its total stays in the ring as a growth hint for the next sync point).
+  int rc;
   c->peer_slot ^= 1;           // every rank renders every frame, so all ranks alternate in step
   rc = frame_enqueue_all(c, intr, pose, to_host);
   if (rc) return rc;
