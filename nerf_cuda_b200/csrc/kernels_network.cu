@@ -26,10 +26,11 @@
 //
 // Numerics: hash indices and fp16 interpolation follow the reference bit-exactly (this TU is built with -fmad=false);
 // the MLP accumulates in fp32 (TMEM) and rounds to fp16 at each layer boundary like the oracle.
+#include <cstdlib>
+
 #include "nrf_device.cuh"
 
-#define NET_THREADS 1024
-#define NET_GROUPS 8
+#define NET_GROUPS_DEFAULT 8   // tile groups (of 128 threads) per persistent CTA; 7 / 6 are experiment variants (NRF_NET_GROUPS)
 #define SMEM_W_BYTES 20480
 #define NET_SMEM (SMEM_W_BYTES + 128)
 // byte offsets of the packed weight matrices inside the 20 KB block
@@ -276,8 +277,8 @@ extern "C" cudaError_t nrf_launch_encode_exp(int variant, int sms, cudaStream_t 
   return cudaGetLastError();
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(NET_THREADS, 1)
+template <int MODE, int NET_GROUPS = NET_GROUPS_DEFAULT>
+__global__ void __launch_bounds__(NET_GROUPS * 128, 1)
 k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__ samples,
           const int* __restrict__ sample_ray, const float4* __restrict__ rays, const uint4* __restrict__ ray_sh,
           int dirs_mode, uint4* __restrict__ enc_io, uint2* __restrict__ out, uint32_t* __restrict__ idx_out,
@@ -322,7 +323,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
   {
     // weights: 20 KB, already in UMMA core-matrix order -> straight copy
     const uint4* src = P.mlp_packed;
-    for (int i = tid; i < SMEM_W_BYTES / 16; i += NET_THREADS) reinterpret_cast<uint4*>(sW)[i] = __ldg(src + i);
+    for (int i = tid; i < SMEM_W_BYTES / 16; i += NET_GROUPS * 128) reinterpret_cast<uint4*>(sW)[i] = __ldg(src + i);
     if (gt == 0) mbar_init(bar, 1);
     if (warp == 0) {
       asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)) : "memory");
@@ -525,17 +526,21 @@ k_network_simt(const __grid_constant__ NetParams P, int n, const uint4* __restri
 }
 
 // ------------------------------------------------------------------------------------------------ host launchers
+template <int MODE, int G>
+static void net_attr() {
+  // 20.6 KB of shared memory per SM; leave the rest of the unified array to L1 (carveout in percent of 228 KB)
+  cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NET_SMEM);
+  cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributePreferredSharedMemoryCarveout, 16);
+}
+static int g_net_groups = NET_GROUPS_DEFAULT;
 static void nrf_network_setup() {
   static bool attr_set = false;
   if (attr_set) return;
-  // 20.6 KB of shared memory per SM; leave the rest of the unified array to L1 (carveout in percent of 228 KB)
-  cudaFuncSetAttribute(k_network<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NET_SMEM);
-  cudaFuncSetAttribute(k_network<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NET_SMEM);
-  cudaFuncSetAttribute(k_network<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NET_SMEM);
-  const int carve = 16;
-  cudaFuncSetAttribute(k_network<0>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-  cudaFuncSetAttribute(k_network<1>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-  cudaFuncSetAttribute(k_network<2>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+  net_attr<0, 8>(); net_attr<1, 8>(); net_attr<2, 8>(); net_attr<2, 7>(); net_attr<2, 6>();
+  if (const char* e = getenv("NRF_NET_GROUPS")) {   // experiment: fewer groups = more registers per thread
+    const int g = atoi(e);
+    if (g == 6 || g == 7 || g == 8) g_net_groups = g;
+  }
   attr_set = true;
 }
 
@@ -546,11 +551,17 @@ extern "C" cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t strea
                                           uint32_t* idx_out, const unsigned long long* n_dev) {
   nrf_network_setup();
   if (n <= 0) return cudaSuccess;
+#define NET_ARGS *P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out, n_dev
   switch (mode) {
-    case 0: k_network<0><<<grid, NET_THREADS, NET_SMEM, stream>>>(*P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out, n_dev); break;
-    case 1: k_network<1><<<grid, NET_THREADS, NET_SMEM, stream>>>(*P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out, n_dev); break;
-    default: k_network<2><<<grid, NET_THREADS, NET_SMEM, stream>>>(*P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out, n_dev); break;
+    case 0: k_network<0, 8><<<grid, 1024, NET_SMEM, stream>>>(NET_ARGS); break;
+    case 1: k_network<1, 8><<<grid, 1024, NET_SMEM, stream>>>(NET_ARGS); break;
+    default:
+      if (g_net_groups == 7) k_network<2, 7><<<grid, 896, NET_SMEM, stream>>>(NET_ARGS);
+      else if (g_net_groups == 6) k_network<2, 6><<<grid, 768, NET_SMEM, stream>>>(NET_ARGS);
+      else k_network<2, 8><<<grid, 1024, NET_SMEM, stream>>>(NET_ARGS);
+      break;
   }
+#undef NET_ARGS
   return cudaGetLastError();
 }
 

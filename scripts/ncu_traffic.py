@@ -4,8 +4,9 @@ import csv, io, json, subprocess, sys
 rep, workload, n_samples = sys.argv[1], sys.argv[2], float(sys.argv[3])
 out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
-hdr, units, r = rows[0], rows[1], rows[2]
+hdr, units = rows[0], rows[1]
 col = {h: i for i, h in enumerate(hdr)}
+r = next(x for x in rows[2:] if 'k_network' in x[col['Kernel Name']])   # the dominant kernel's launch
 def val(m, scale_unit=True):
     v = float(r[col[m]].replace(",", ""))
     u = units[col[m]]
