@@ -9,7 +9,8 @@
 //   decompose_network_in_and_out             include/nerf-cuda/render_utils.h:308-334
 // and removes every global-memory round trip between them: only {r,g,b,sigma} (4 halves) per sample reach HBM.
 //
-// Shape of the kernel (k_network): ONE persistent CTA per SM with 1024 threads = 8 tile groups of 128 threads; a group
+// Shape of the kernel (k_network): ONE persistent CTA per SM with 7 tile groups of 128 threads (896 threads x 72
+// registers; 8 groups x 64 registers spill and measure 3-4 % slower, 6 groups lose more to occupancy); a group
 // processes one 128-sample tile at a time (UMMA M = 128) and thread t of the group owns sample row t end to end
 // (gather -> A-operand row t -> accumulator lane t).  All groups share one 20 KB copy of the weights in shared memory
 // (pre-packed on the host into the K-major SWIZZLE_NONE core-matrix order); nothing else lives in shared memory, so
@@ -532,7 +533,7 @@ static void net_attr() {
   cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NET_SMEM);
   cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributePreferredSharedMemoryCarveout, 16);
 }
-static int g_net_groups = NET_GROUPS_DEFAULT;
+static int g_net_groups = 7;   // measured on B200 (C3): 7 groups = 896 threads x 72 registers, no spills: 3-4 % faster than 8 x 64 (spills), 6 is slower again
 static void nrf_network_setup() {
   static bool attr_set = false;
   if (attr_set) return;
