@@ -257,6 +257,7 @@ def gpu_arm(args):
         smp_total = float(np.mean(samples))
     rays = W * H
     pk = peaks()
+    table_mb = 2 * int(syn.level_table(sc.desc)[0][-1]) * 2 / 1e6
     out = None
     if rank == 0:
         net = float(np.mean(net_ms))
@@ -277,14 +278,15 @@ def gpu_arm(args):
                            f"32x32-pixel tiles round-robin over {world} ranks, NCCL gather of packed u8 tiles to rank 0"),
                        "samples_per_frame": smp_total, "samples_per_ray": smp_total / rays,
                        "l2": f"inputs larger than L2: each frame streams {smp_total / world * 60 / 1e6:.0f} MB of sample records per GPU "
-                             f"and the pose changes every step; the {2 * int(syn.level_table(sc.desc)[0][-1]) * 2 / 1e6:.1f} MB hash table is L2-resident by design"},
+                             f"and the pose changes every step; the {table_mb:.1f} MB hash table is "
+                             + ("L2-resident by design" if table_mb < 100 else "far larger than the 126 MB L2 (HBM-resident gather)")},
             "e2e": {"value": rays * args.steps / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": 80, "d2h_bytes_per_step": rays * 4 + 8 if (world == 1 or peer) else rays * 3 + 8},
             "gpu_launches": 5 * args.steps,
             "clocks": clocks,
             "roofline": {"kernel": "k_network<2> (hash-grid gather + tcgen05 MLP, fused)", "bound": "hbm",
                          "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s", "frac": achieved / pk["hbm"],
-                         **ncu_traffic(s_k), "peak_source": pk["src"] + " (HBM copy; the table is L2-resident, so >1 is possible)",
+                         **(ncu_traffic(s_k) if table_mb < 100 else {"traffic": None}), "peak_source": pk["src"] + (" (HBM copy; the table is L2-resident, so >1 is possible)" if table_mb < 100 else " (HBM copy)"),
                          "algorithmic_bytes_per_sample": GATHER_BYTES_PER_SAMPLE + STREAM_BYTES_PER_SAMPLE,
                          "samples_per_launch": s_k, "ms_per_launch": net,
                          "mlp_tflops_in_fused": s_k * MLP_FLOP_PER_SAMPLE / (net * 1e-3) / 1e12,
