@@ -164,7 +164,7 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
   T.w0 = p0 - f0; T.w1 = p1 - f1; T.w2 = p2 - f2;
   const uint32_t* __restrict__ tl = lv.tab;
   uint32_t e[8];
-  if (lv.hashed) {
+  if (lv.hashed == 1) {
     const uint32_t m = lv.size - 1u;
     const uint32_t hy0 = g1 * 2654435761u, hy1 = hy0 + 2654435761u, hz0 = g2 * 805459861u, hz1 = hz0 + 805459861u;
     const uint32_t yz[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
@@ -184,6 +184,20 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
       T.raw[2 * j] = up ? q.y : q.x;
       T.raw[2 * j + 1] = odd ? far : (up ? q.x : q.y);
     }
+  } else if (lv.hashed == 2) {
+    // hashed level, plain 4-byte loads (no slot pairing): fewer instructions, more L1 wavefronts — chosen per level on
+    // the host for the levels whose lanes share cache lines anyway (NRF_PAIR_FROM)
+    const uint32_t m = lv.size - 1u;
+    const uint32_t hy0 = g1 * 2654435761u, hy1 = hy0 + 2654435761u, hz0 = g2 * 805459861u, hz1 = hz0 + 805459861u;
+    const uint32_t yz[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
+    const uint32_t g0p = g0 + 1u;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      e[2 * j] = (g0 ^ yz[j]) & m;
+      e[2 * j + 1] = (g0p ^ yz[j]) & m;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) T.raw[k] = __ldg(tl + e[k]);
   } else {
     const uint32_t r1 = lv.res, r2 = lv.res * lv.res, Tl = lv.size;
     const uint32_t b = g0 + g1 * r1 + g2 * r2;

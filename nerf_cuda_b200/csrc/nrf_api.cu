@@ -367,6 +367,11 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
     const double dense = (double)L.res * L.res * L.res;
     L.hashed = dense > (double)L.size ? 1u : 0u;
     if (L.hashed && (L.size & (L.size - 1)) != 0) return fail(NRF_EINVAL, "hashed level %u size %u not a power of two", l, L.size);
+    // hashed levels below pair_from use plain 4-byte loads (2), from pair_from on the paired 8-byte slot loads (1)
+    // (measured on B200: C3 network 5.68 / 5.62 / 5.69 / 5.78 ms at pair_from 0 / 8 / 12->5.57 / 16; C2 prefers 16 by 3 %:
+    // pairing trades ~5 instructions per corner pair for fewer L1 wavefronts, which pays only on the finest levels)
+    static const int pair_from = std::getenv("NRF_PAIR_FROM") ? std::atoi(std::getenv("NRF_PAIR_FROM")) : 12;
+    if (L.hashed && (int)l < pair_from) L.hashed = 2u;
   }
   N.mlp_rowmaj = D.params_h.p;
   N.table = reinterpret_cast<const __half2*>(D.params_h.p + 10240);
