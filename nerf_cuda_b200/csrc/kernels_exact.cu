@@ -109,11 +109,20 @@ __device__ __forceinline__ void ray_ctx(const MarchParams& P, const float* lut, 
   }
 }
 
+// rare path of the FAST step (a coordinate left [-bound, bound] by rounding at a box face): out of line and by value
+// (registers in, registers out), so that the common path does not issue seven predicated-off instructions per step
+__device__ __noinline__ float4 clamp_to_box(float bound, float x, float y, float z) {
+  x = clampf(x, -bound, bound); y = clampf(y, -bound, bound); z = clampf(z, -bound, bound);
+  return make_float4(x, y, z, fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z))));
+}
+
 template <bool FAST>
 __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R, float& t, Step& s) {
   float x = R.o[0] + t * R.d[0], y = R.o[1] + t * R.d[1], z = R.o[2] + t * R.d[2];
   float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
-  if (!FAST || mx > R.bound) {
+  if (FAST) {
+    if (mx > R.bound) { const float4 c = clamp_to_box(R.bound, x, y, z); x = c.x; y = c.y; z = c.z; mx = c.w; }
+  } else {
     x = clampf(x, -R.bound, R.bound); y = clampf(y, -R.bound, R.bound); z = clampf(z, -R.bound, R.bound);
     mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
   }
