@@ -85,11 +85,11 @@ __device__ __forceinline__ float lds_f32(uint32_t saddr) {
 // The march loop is issue-bound and ptxas re-reads kernel parameters from the constant bank on every use (one LDC/LDCU
 // issue slot each, ~10 per step).  The per-frame constants the FAST step needs are therefore staged behind the table in
 // shared memory (load_lut) and read ONCE per ray with a volatile shared load, which pins them in vector registers.
-#define LUT_CONST 12  // o[3], bound, dt_gamma, halfH, hm1, t_lo, t_hi, H, C-1, (pad) behind the H+1 table entries
+#define LUT_CONST 16  // o[3], bound, dt_gamma, halfH, hm1, t_lo, t_hi, H, C-1, dt_min, dt_max, (pad) behind the H+1 table entries
 struct RayCtx {
   float d[3], rd[3];
   uint32_t lut_a[3];  // shared-memory byte address of lut[1 - signbit(d_a)]: entry n + 1 (d >= +0) or n (sign set)
-  float o[3], bound, dt_gamma, halfH, hm1, t_lo, t_hi;   // pinned copies of per-frame constants
+  float o[3], bound, dt_gamma, halfH, hm1, t_lo, t_hi, dt_min, dt_max;   // pinned copies of per-frame constants
   uint32_t H;
   int cm1;
 };
@@ -100,6 +100,7 @@ __device__ __forceinline__ void ray_ctx(const MarchParams& P, const float* lut, 
   R.bound = lds_f32(cb + 12); R.dt_gamma = lds_f32(cb + 16); R.halfH = lds_f32(cb + 20); R.hm1 = lds_f32(cb + 24);
   R.t_lo = lds_f32(cb + 28); R.t_hi = lds_f32(cb + 32);
   R.H = __float_as_uint(lds_f32(cb + 36)); R.cm1 = (int)__float_as_uint(lds_f32(cb + 40));
+  R.dt_min = lds_f32(cb + 44); R.dt_max = lds_f32(cb + 48);
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
     R.d[a] = d[a];
@@ -151,7 +152,7 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
   const bool occ = (__ldg(P.occupancy + (cell >> 5)) >> (cell & 31u)) & 1u;
   if (occ) {
     s.x = x; s.y = y; s.z = z;
-    const float dt = clampf(t * P.dt_gamma, P.dt_min, P.dt_max);
+    const float dt = clampf(t * R.dt_gamma, R.dt_min, R.dt_max);
     t += dt;
     s.dt = dt;
     s.cell = cell;
@@ -174,7 +175,7 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
     do { t = __fmaf_rn(t, R.dt_gamma, t); } while (t < tt);   // dt_min <= t*dt_gamma <= dt_max on every step taken
   } else {
     do {
-      const float dt = clampf(t * P.dt_gamma, P.dt_min, P.dt_max);
+      const float dt = clampf(t * R.dt_gamma, R.dt_min, R.dt_max);
       t += dt;
     } while (t < tt);
   }
@@ -189,7 +190,7 @@ __device__ __forceinline__ void load_lut(const MarchParams& P, float* lut) {
     float* c = lut + P.H + 1;
     c[0] = P.o[0]; c[1] = P.o[1]; c[2] = P.o[2]; c[3] = P.bound; c[4] = P.dt_gamma;
     c[5] = 0.5f * (float)P.H; c[6] = (float)(P.H - 1); c[7] = P.t_lo; c[8] = P.t_hi;
-    c[9] = __uint_as_float(P.H); c[10] = __uint_as_float(P.C - 1u); c[11] = 0.f;
+    c[9] = __uint_as_float(P.H); c[10] = __uint_as_float(P.C - 1u); c[11] = P.dt_min; c[12] = P.dt_max;
   }
   __syncthreads();
 }
