@@ -243,6 +243,13 @@ def gpu_arm(args):
         frame(i, False)
     ms_dev, _, _ = timed(False, args.steps, args.warmup)
     ms_e2e, net_ms, samples = timed(True, args.steps, max(3, args.warmup // 2), collect_stats=True)
+    batch_rps = None
+    if world == 1:   # the same host-in / host-out work through the pipelined batch call (render_server --batch)
+        pb = np.stack([poses[(args.warmup + i) % len(poses)] for i in range(args.steps)])
+        r.render_batch(intr, pb[: min(len(pb), len(poses))])
+        tb = time.perf_counter()
+        r.render_batch(intr, pb)
+        batch_rps = W * H * len(pb) / (time.perf_counter() - tb)
     clocks = sampler.stop() if rank == 0 else None
     # stage rooflines on the last frame's resident samples (kernel timed alone -> burst peaks)
     stage = {}
@@ -281,7 +288,7 @@ def gpu_arm(args):
                              f"and the pose changes every step; the {table_mb:.1f} MB hash table is "
                              + ("L2-resident by design" if table_mb < 100 else "far larger than the 126 MB L2 (HBM-resident gather)")},
             "e2e": {"value": rays * args.steps / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
-                    "h2d_bytes_per_step": 80, "d2h_bytes_per_step": rays * 4 + 8 if (world == 1 or peer) else rays * 3 + 8},
+                    "batch_call_value": batch_rps, "h2d_bytes_per_step": 80, "d2h_bytes_per_step": rays * 4 + 8 if (world == 1 or peer) else rays * 3 + 8},
             "gpu_launches": 5 * args.steps,
             "clocks": clocks,
             "roofline": {"kernel": "k_network<2> (hash-grid gather + tcgen05 MLP, fused)", "bound": "hbm",

@@ -237,6 +237,9 @@ struct nrf_ctx {
   uint8_t* peer_host = nullptr;   // pinned W*H*4, destination rank only
   uint8_t* rgb_host = nullptr;    // pinned, W*H*3 (full frame when n_shards == 1, else this shard's packed tiles)
   uint8_t* depth_host = nullptr;  // pinned, W*H
+  uint8_t* batch_stage[2] = {nullptr, nullptr};   // pinned staging of nrf_render_batch's two-deep pipeline
+  cudaEvent_t batch_ev[2] = {nullptr, nullptr};
+  size_t batch_bytes = 0;
   nrf_stats stats{};
   // a frame that was enqueued without a host sync (its sample total is still unchecked against the buffer capacity)
   bool pending = false, pending_to_host = false;
@@ -308,6 +311,10 @@ extern "C" int nrf_destroy(nrf_ctx* c) {
     else if (c->peer_owned) cudaFree(c->peer_frame);
   }
   if (c->peer_host) cudaFreeHost(c->peer_host);
+  for (int k = 0; k < 2; ++k) {
+    if (c->batch_stage[k]) cudaFreeHost(c->batch_stage[k]);
+    if (c->batch_ev[k]) cudaEventDestroy(c->batch_ev[k]);
+  }
   for (Device& D : c->devs) free_device(D);
   if (c->rgb_host) cudaFreeHost(c->rgb_host);
   if (c->depth_host) cudaFreeHost(c->depth_host);
@@ -750,16 +757,68 @@ extern "C" int nrf_render_frame_device(nrf_ctx* c, const float intr[4], const fl
   return render_common(c, intr, pose, false, false);
 }
 
+// Batch of poses (render_server --batch): a two-deep pipeline.  Frame i is enqueued (no host sync), its u8 pixels are
+// copied to one of two pinned staging buffers on the same stream, and while the GPU renders frame i+1 the host copies
+// frame i-1 out of the other staging buffer into the caller's memory.  A frame whose sample total exceeded the buffers
+// (possible only while the buffers are still growing) is rendered again synchronously at the end.
 extern "C" int nrf_render_batch(nrf_ctx* c, const float intr[4], const float* poses, int n_poses, uint8_t* rgb_out) {
-  if (!rgb_out || n_poses < 0) return fail(NRF_EINVAL, "nrf_render_batch: bad arguments");
+  if (!c || !intr || !rgb_out || n_poses < 0 || (n_poses > 0 && !poses)) return fail(NRF_EINVAL, "nrf_render_batch: bad arguments");
   int n_local = 0;
   int rc = nrf_local_rays(c, &n_local);
   if (rc) return rc;
+  if (!c->loaded) return fail(NRF_ESTATE, "render_batch before reload_network_from_file");
   const size_t frame_bytes = (c->n_shards == 1 ? (size_t)c->W * c->H : (size_t)n_local) * 3;
-  for (int i = 0; i < n_poses; ++i) {
-    rc = render_common(c, intr, poses + (size_t)i * 16, true, true);
+  if (n_poses == 0) return NRF_OK;
+  // the first frame synchronously: it sizes the sample buffers
+  rc = render_common(c, intr, poses, true, true);
+  if (rc) return rc;
+  std::memcpy(rgb_out, c->rgb_host, frame_bytes);
+  if (n_poses == 1) return NRF_OK;
+  Device& D0 = c->devs[0];
+  CU(cudaSetDevice(D0.dev));
+  if (c->batch_bytes < frame_bytes) {
+    for (int k = 0; k < 2; ++k) {
+      if (c->batch_stage[k]) cudaFreeHost(c->batch_stage[k]);
+      c->batch_stage[k] = nullptr;
+      CU(cudaMallocHost(&c->batch_stage[k], frame_bytes));
+      if (!c->batch_ev[k]) CU(cudaEventCreateWithFlags(&c->batch_ev[k], cudaEventDisableTiming));
+    }
+    c->batch_bytes = frame_bytes;
+  }
+  std::vector<int> redo;
+  unsigned fno[2][8] = {};   // per staging slot: frame_no of every device when the frame was enqueued
+  auto collect = [&](int j) -> int {   // frame j has landed in staging slot j & 1
+    const int slot = j & 1;
+    CU(cudaEventSynchronize(c->batch_ev[slot]));
+    bool over = false;
+    for (size_t g = 0; g < c->devs.size(); ++g) over |= c->devs[g].total_h[fno[slot][g] & 3u] > c->devs[g].samples.n;
+    if (over) redo.push_back(j);
+    else std::memcpy(rgb_out + (size_t)j * frame_bytes, c->batch_stage[slot], frame_bytes);
+    return NRF_OK;
+  };
+  for (int i = 1; i < n_poses; ++i) {
+    const int slot = i & 1;
+    if (i >= 3) { rc = collect(i - 2); if (rc) return rc; }   // frees this staging slot
+    c->peer_slot ^= 1;
+    rc = frame_enqueue_all(c, intr, poses + (size_t)i * 16, false);
     if (rc) return rc;
-    std::memcpy(rgb_out + (size_t)i * frame_bytes, c->rgb_host, frame_bytes);
+    for (size_t g = 0; g < c->devs.size() && g < 8; ++g) fno[slot][g] = c->devs[g].frame_no;
+    CU(cudaSetDevice(D0.dev));
+    for (size_t g = 1; g < c->devs.size(); ++g) CU(cudaStreamWaitEvent(D0.stream, c->devs[g].done, 0));
+    CU(cudaMemcpyAsync(c->batch_stage[slot], D0.rgb_u8.p, frame_bytes, cudaMemcpyDeviceToHost, D0.stream));
+    CU(cudaEventRecord(c->batch_ev[slot], D0.stream));
+    c->pending = true;
+    c->pending_to_host = false;
+    std::memcpy(c->pending_intr, intr, 16);
+    std::memcpy(c->pending_pose, poses + (size_t)i * 16, 64);
+  }
+  for (int j = std::max(1, n_poses - 2); j < n_poses; ++j) { rc = collect(j); if (rc) return rc; }
+  rc = frame_resolve(c);   // validates the last frame, grows the buffers to the largest total seen
+  if (rc) return rc;
+  for (int j : redo) {
+    rc = render_common(c, intr, poses + (size_t)j * 16, true, true);
+    if (rc) return rc;
+    std::memcpy(rgb_out + (size_t)j * frame_bytes, c->rgb_host, frame_bytes);
   }
   return NRF_OK;
 }

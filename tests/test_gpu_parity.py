@@ -418,3 +418,25 @@ def test_async_frames_and_buffer_regrowth(pair):
     assert all(np.array_equal(x, y) for x, y in zip(fa, ref["a"][1:4])) and r2.stats().n_samples == ref["a"][4]
     assert np.array_equal(r2.render_frame(intr, pb)[0], ref["b"][0])
     r2.close()
+
+
+def test_render_batch_pipeline_matches_single_frames(pair):
+    """nrf_render_batch (render_server --batch): the two-deep pipeline (frame i+1 renders while frame i is copied out)
+    must return exactly the frames of one-at-a-time render_frame calls — also from a fresh context whose sample buffers
+    are still growing (frames that overflowed are rendered again), and for 1- and 2-pose batches."""
+    name, sc, r, O = pair
+    W, H = 72, 40
+    intr = syn.intrinsics(W, H)
+    poses = [syn.look_at_pose(syn.camera_radius(name), 20.0, az) for az in (0.0, 200.0, 75.0, 310.0, 140.0)]
+    r.set_shard(0, 1)
+    r.set_resolution((W, H))
+    ref = [r.render_frame(intr, p)[0].copy() for p in poses]
+    r2 = NerfRender(1)
+    r2.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    r2.set_resolution((W, H))
+    for n in (5, 1, 2, 5):
+        out = r2.render_batch(intr, np.stack(poses[:n]))
+        assert out.shape[0] == n
+        for k in range(n):
+            assert np.array_equal(out[k].reshape(H, W, 3), ref[k]), (n, k)
+    r2.close()
