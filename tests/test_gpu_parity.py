@@ -440,3 +440,21 @@ def test_render_batch_pipeline_matches_single_frames(pair):
         for k in range(n):
             assert np.array_equal(out[k].reshape(H, W, 3), ref[k]), (n, k)
     r2.close()
+
+
+@pytest.mark.parametrize("W,H", [(50, 37), (33, 5), (8, 4), (100, 31)])
+def test_u8_frame_is_the_cast_of_the_float_frame(pair, W, H):
+    """The u8 frame (packed 4-byte word stores when W % 4 == 0, byte stores otherwise, edge patches partly outside the
+    image) must be exactly (unsigned char)(255.0 * v) of the float frame the same call produced, pixel by pixel
+    (nerf_render.cu:355-358), and the float frame must match the oracle — for widths that are not multiples of the
+    8-pixel patch, of 4, or of anything."""
+    name, sc, r, O = pair
+    intr, pose = syn.intrinsics(W, H), syn.look_at_pose(syn.camera_radius(name), 20.0, 77.0)
+    r.set_shard(0, 1)
+    r.set_resolution((W, H))
+    rgb_u8, dep_u8 = (a.copy() for a in r.render_frame(intr, pose))
+    rgb, dep, cnt = r.float_frame()
+    cast = lambda v: np.clip(np.floor(255.0 * v.astype(np.float64)), 0, 255).astype(np.uint8)
+    assert np.array_equal(rgb_u8.reshape(-1, 3), cast(rgb)) and np.array_equal(dep_u8.reshape(-1), cast(dep))
+    rgb2, dep2, cnt2 = O.render(intr, pose, W, H)
+    assert np.array_equal(cnt, cnt2) and np.abs(rgb - rgb2).max() <= IMG_TOL
