@@ -196,8 +196,12 @@ __device__ __forceinline__ void load_lut(const MarchParams& P, float* lut) {
 }
 
 // Whole-ray count; t_first = the t at which the first sample was taken (pass 2 restarts there: the march state is t)
+// tc (may be null): this ray's column of the sample-t cache — the t of its first NRF_TCACHE samples, entry k at
+// tc[32*k] (patch-interleaved like the sample list), so that pass 2 replays the samples instead of marching the
+// empty space between them a second time.
 template <bool FAST>
-__device__ __forceinline__ int count_ray_t(const MarchParams& P, const RayCtx& R, float near, float far, float& t_first) {
+__device__ __forceinline__ int count_ray_t(const MarchParams& P, const RayCtx& R, float near, float far, float& t_first,
+                                           float* __restrict__ tc) {
   float t = near;
   int c = 0;
   t_first = near;
@@ -206,16 +210,17 @@ __device__ __forceinline__ int count_ray_t(const MarchParams& P, const RayCtx& R
     const float t0 = t;
     if (march_step<FAST>(P, R, t, s)) {
       if (c == 0) t_first = t0;
+      if (tc && c < NRF_TCACHE) tc[32 * c] = t0;
       ++c;
     }
   }
   return c;
 }
 __device__ __forceinline__ int count_ray(const MarchParams& P, const float* lut, const float d[3], float near, float far,
-                                         float& t_first) {
+                                         float& t_first, float* __restrict__ tc = nullptr) {
   RayCtx R;
   ray_ctx(P, lut, d, R);
-  return P.fast ? count_ray_t<true>(P, R, near, far, t_first) : count_ray_t<false>(P, R, near, far, t_first);
+  return P.fast ? count_ray_t<true>(P, R, near, far, t_first, tc) : count_ray_t<false>(P, R, near, far, t_first, tc);
 }
 
 // block-wide sum / exclusive scan helpers (128 threads, warp shuffles)
@@ -245,10 +250,11 @@ __device__ __forceinline__ void block_total(int c, int* __restrict__ block_sums)
 extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, 8)
 k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, float4* __restrict__ rays,
              float2* __restrict__ far_tf, int* __restrict__ counts, int* __restrict__ block_sums,
-             uint4* __restrict__ ray_sh) {
+             uint4* __restrict__ ray_sh, float* __restrict__ tcache) {
   __shared__ float lut[NRF_MAX_GRID + 1 + LUT_CONST];
   load_lut(P, lut);
   const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
+  float* tc = tcache ? tcache + (size_t)(q >> 5) * (32 * NRF_TCACHE) + (q & 31) : nullptr;
   int c = 0;
   if (q < n_local) {
     const int p = shard_pixel(map, q);
@@ -256,7 +262,7 @@ k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, f
     if (p >= 0) {
       ray_dir(P, p, d);
       near_far(P, d, near, far);
-      c = count_ray(P, lut, d, near, far, tf);
+      c = count_ray(P, lut, d, near, far, tf, tc);
     }
     rays[q] = make_float4(d[0], d[1], d[2], near);
     far_tf[q] = make_float2(far, tf);
@@ -345,7 +351,8 @@ extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, 8)
 k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays, const float2* __restrict__ far_tf,
        const int* __restrict__ counts, const int* __restrict__ block_bases, int* __restrict__ warp_base,
        float4* __restrict__ samples, float* __restrict__ t_after, int* __restrict__ sample_ray,
-       float* __restrict__ dbg, const long long* __restrict__ dbg_offsets, long long capacity) {
+       float* __restrict__ dbg, const long long* __restrict__ dbg_offsets, long long capacity,
+       const float* __restrict__ tcache) {
   __shared__ float lut[NRF_MAX_GRID + 1 + LUT_CONST];
   __shared__ int wsum[RAYS_BLOCK / 32];
   __shared__ uint32_t died[RAYS_BLOCK / 32][NRF_MAX_STEPS_D];
@@ -384,6 +391,28 @@ k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ 
   const long long dbg0 = dbg ? dbg_offsets[q] : 0;
   Step s;
   const bool fast = P.fast;
+  if (tcache) {
+    // replay the cached samples: position, dt and t_after are the occupied branch of march_step evaluated at the
+    // cached t (the clamp to the box is the identity inside it, so both march variants give these same values)
+    const float* tc = tcache + (size_t)(q >> 5) * (32 * NRF_TCACHE) + lane;
+    const int nrep = min(c_total, NRF_TCACHE);
+    float t0 = __ldg(tc);
+    for (; c < nrep; ++c) {
+      const float tn = (c + 1 < nrep) ? __ldg(tc + 32 * (c + 1)) : 0.f;
+      const float x = clampf(R.o[0] + t0 * R.d[0], -R.bound, R.bound);
+      const float y = clampf(R.o[1] + t0 * R.d[1], -R.bound, R.bound);
+      const float z = clampf(R.o[2] + t0 * R.d[2], -R.bound, R.bound);
+      const float dt = clampf(t0 * R.dt_gamma, R.dt_min, R.dt_max);
+      t = t0 + dt;
+      const long long k = off + __popc(alive & lt);
+      samples[k] = make_float4(P.pos_w * x + 0.5f, P.pos_w * y + 0.5f, P.pos_w * z + 0.5f, dt);
+      t_after[k] = t;
+      sample_ray[k] = q;
+      off += __popc(alive);
+      alive &= ~died[warp][c];
+      t0 = tn;
+    }
+  }
   while (t < far && c < c_total) {
     if (!(fast ? march_step<true>(P, R, t, s) : march_step<false>(P, R, t, s))) continue;
     const long long k = off + __popc(alive & lt);

@@ -29,14 +29,14 @@
 // kernels (kernels_exact.cu, kernels_network.cu, kernels_composite.cu)
 extern "C" {
 __global__ void k_rays_count(const MarchParams P, ShardMap map, int n_local, float4* rays, float2* far_tf, int* counts,
-                             int* block_sums, uint4* ray_sh);
+                             int* block_sums, uint4* ray_sh, float* tcache);
 __global__ void k_rays_given_pixels(const MarchParams P, int pix0, int n, float4* rays, float* fars);
 __global__ void k_count_given(const MarchParams P, int n, const float4* rays, float2* far_tf, int* counts,
                               int* block_sums);
 __global__ void k_scan_blocks(int* block_sums, int n_blocks, unsigned long long* total);
 __global__ void k_emit(const MarchParams P, int n, const float4* rays, const float2* far_tf, const int* counts,
                        const int* block_bases, int* warp_base, float4* samples, float* t_after, int* sample_ray,
-                       float* dbg, const long long* dbg_offsets, long long capacity);
+                       float* dbg, const long long* dbg_offsets, long long capacity, const float* tcache);
 __global__ void k_build_occupancy(const float* grid, uint32_t n_cells, float thresh, uint32_t* bits);
 __global__ void k_cast_half(const float* in, __half* out, size_t n);
 __global__ void k_accumulate(int n, const float4* frame, float4* accum, float sample_count, int color_space);
@@ -207,7 +207,7 @@ struct Device {
   DevBuf<float4> rays, samples;
   DevBuf<uint4> ray_sh;
   DevBuf<float2> far_tf;
-  DevBuf<float> t_after, rgb_f32, depth_f32;
+  DevBuf<float> t_after, rgb_f32, depth_f32, tcache;
   DevBuf<int> counts, warp_base, block_sums, sample_ray, used;
   DevBuf<uint2> sample_out;
   DevBuf<uint8_t> rgb_u8, depth_u8;
@@ -229,6 +229,8 @@ struct nrf_ctx {
   bool loaded = false;
   int W = 0, H = 0;
   int shard = 0, n_shards = 1;    // process-level sharding (one process per GPU); requires a single-device context
+  // sample-t cache between the two march passes (NRF_TCACHE floats per ray; NRF_NO_TCACHE=1 re-marches instead)
+  bool use_tcache = std::getenv("NRF_NO_TCACHE") == nullptr;
   // peer frame of the one-process-per-GPU mode: ONE W*H*4-byte buffer (rgb W*H*3 | depth W*H) owned by the destination
   // rank and mapped into every other rank through CUDA IPC; composites store their pixels straight into it over NVLink
   uint8_t* peer_frame = nullptr;  // device pointer valid in THIS process (own allocation or IPC mapping)
@@ -290,7 +292,7 @@ extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
 static void free_device(Device& D) {
   cudaSetDevice(D.dev);
   D.params_h.release(); D.mlp_packed.release(); D.occupancy.release(); D.density_grid.release(); D.div_lut.release();
-  D.rays.release(); D.ray_sh.release(); D.samples.release(); D.far_tf.release(); D.t_after.release(); D.rgb_f32.release();
+  D.rays.release(); D.ray_sh.release(); D.tcache.release(); D.samples.release(); D.far_tf.release(); D.t_after.release(); D.rgb_f32.release();
   D.depth_f32.release(); D.counts.release(); D.warp_base.release(); D.block_sums.release();
   D.sample_ray.release(); D.used.release(); D.sample_out.release(); D.rgb_u8.release(); D.depth_u8.release();
   D.total.release(); D.enc.release(); D.idx.release(); D.dbg.release();
@@ -536,6 +538,7 @@ extern "C" int nrf_set_resolution(nrf_ctx* c, int W, int H) {
     CU(D.rays.ensure(N)); CU(D.ray_sh.ensure(2 * N)); CU(D.far_tf.ensure(N)); CU(D.counts.ensure(N)); CU(D.warp_base.ensure((N + 31) / 32));
     CU(D.block_sums.ensure(nb)); CU(D.used.ensure(N)); CU(D.rgb_f32.ensure(N * 3)); CU(D.depth_f32.ensure(N));
     CU(D.total.ensure(4));
+    if (c->use_tcache) CU(D.tcache.ensure(((N + 31) / 32) * 32 * NRF_TCACHE));
     // u8 outputs: whole-frame contexts keep ONE frame in pixel order on device 0; a sharded context keeps its packed tiles
     if (g == 0) {
       const size_t px = c->n_shards == 1 ? (size_t)W * H : N;
@@ -633,7 +636,7 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
   CU(cudaEventRecord(D.ev[0], D.stream));
   if (D.n_local > 0) {
     k_rays_count<<<nb, 128, 0, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
-                                          D.ray_sh.p);
+                                          D.ray_sh.p, D.tcache.p);
     CU(cudaGetLastError());
   }
   k_scan_blocks<<<1, 1024, 0, D.stream>>>(D.block_sums.p, D.n_local > 0 ? nb : 0, D.total.p);
@@ -644,7 +647,7 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
   if (D.n_local > 0) {
     k_emit<<<nb, 128, 0, D.stream>>>(D.march, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
                                     D.warp_base.p, D.samples.p, D.t_after.p, D.sample_ray.p, nullptr, nullptr,
-                                    (long long)cap);
+                                    (long long)cap, D.tcache.p);
     CU(cudaGetLastError());
   }
   CU(cudaEventRecord(D.ev[2], D.stream));
@@ -952,7 +955,7 @@ extern "C" int nrf_probe_march(nrf_ctx* c, int n, const float rays_o[3], const f
       CU(doff.ensure(n));
       CU(cudaMemcpyAsync(doff.p, ho.data(), (size_t)n * 8, cudaMemcpyHostToDevice, D.stream));
       CU(smp.ensure(S)); CU(ta.ensure(S)); CU(sray.ensure(S)); CU(dbg.ensure(S * 8));
-      k_emit<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p, wb.p, smp.p, ta.p, sray.p, dbg.p, doff.p, (long long)S);
+      k_emit<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p, wb.p, smp.p, ta.p, sray.p, dbg.p, doff.p, (long long)S, nullptr);
       CU(cudaGetLastError());
       CU(cudaMemcpyAsync(samples, dbg.p, (size_t)S * 32, cudaMemcpyDeviceToHost, D.stream));
       CU(cudaStreamSynchronize(D.stream));

@@ -11,6 +11,7 @@
 //   samples    : float4[S] {u,v,w (position normalised to [0,1]), dt} + float[S] t_after + int[S] ray, in
 //                WARP-INTERLEAVED order: for each 32-ray patch, step k of all its live rays, then step k+1, ...
 //   warp_base  : int[N/32] first sample of each patch
+//   tcache     : float[N/32][NRF_TCACHE][32] t of each ray's first NRF_TCACHE samples (pass 1 -> pass 2)
 //   ray_sh     : uint4[2N] the 16 fp16 SH coefficients of every ray's direction
 //   sample_out : uint2[S]  four halves {r,g,b,sigma}
 #pragma once
@@ -21,6 +22,7 @@
 #define NRF_L 16          // hash-grid levels (base.json)
 #define NRF_TILE 128      // samples per MMA tile == UMMA M
 #define NRF_MAX_STEPS_D 1024
+#define NRF_TCACHE 64     // sample t values cached per ray between the two march passes (kernels_exact.cu)
 
 struct LevelInfo {
   uint32_t offset;  // first entry of the level (in entries)

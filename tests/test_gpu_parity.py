@@ -458,3 +458,30 @@ def test_u8_frame_is_the_cast_of_the_float_frame(pair, W, H):
     assert np.array_equal(rgb_u8.reshape(-1, 3), cast(rgb)) and np.array_equal(dep_u8.reshape(-1), cast(dep))
     rgb2, dep2, cnt2 = O.render(intr, pose, W, H)
     assert np.array_equal(cnt, cnt2) and np.abs(rgb - rgb2).max() <= IMG_TOL
+
+
+def test_sample_t_cache_replay_and_resume(pair, monkeypatch):
+    """Pass 2 of the march replays each ray's first NRF_TCACHE (64) cached sample positions and resumes marching after
+    them.  With every cell occupied each step is a sample (hundreds per ray), so replay, the hand-over and the resumed
+    march are all exercised: the frame must match the oracle, and equal — bit for bit, sample total included — the
+    frame of a context that re-marches instead (NRF_NO_TCACHE, read when the context is created)."""
+    name, sc, r, O = pair
+    W, H = 40, 24
+    intr, pose = syn.intrinsics(W, H), syn.look_at_pose(syn.camera_radius(name), 20.0, 33.0)
+    grid = np.ones_like(sc.grid)
+    frames = []
+    for no_cache in (False, True):
+        if no_cache:
+            monkeypatch.setenv("NRF_NO_TCACHE", "1")
+        r2 = NerfRender(1)
+        r2.load_raw(sc.desc, sc.params, grid, sc.aabb)
+        r2.set_resolution((W, H))
+        u8 = r2.render_frame(intr, pose)[0].copy()
+        frames.append((u8,) + tuple(x.copy() for x in r2.float_frame()) + (r2.stats().n_samples,))
+        r2.close()
+    a, b = frames
+    assert a[4] == b[4] and a[4] > 64 * W * H // 4
+    assert all(np.array_equal(x, y) for x, y in zip(a[:4], b[:4]))
+    O2 = orc.Oracle(sc.desc, sc.params, grid, sc.aabb)
+    rgb2, dep2, cnt2 = O2.render(intr, pose, W, H)
+    assert np.array_equal(a[3], cnt2) and np.abs(a[1] - rgb2).max() <= IMG_TOL
