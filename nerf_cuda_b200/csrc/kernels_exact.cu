@@ -85,13 +85,14 @@ __device__ __forceinline__ float lds_f32(uint32_t saddr) {
 // The march loop is issue-bound and ptxas re-reads kernel parameters from the constant bank on every use (one LDC/LDCU
 // issue slot each, ~10 per step).  The per-frame constants the FAST step needs are therefore staged behind the table in
 // shared memory (load_lut) and read ONCE per ray with a volatile shared load, which pins them in vector registers.
-#define LUT_CONST 16  // o[3], bound, dt_gamma, halfH, hm1, t_lo, t_hi, H, C-1, dt_min, dt_max, (pad) behind the H+1 table entries
+#define LUT_CONST 16  // o[3], bound, dt_gamma, halfH, hm1, t_lo, t_hi, H, C-1, dt_min, dt_max, occupancy pointer (2), (pad) behind the H+1 table entries
 struct RayCtx {
   float d[3], rd[3];
   uint32_t lut_a[3];  // shared-memory byte address of lut[1 - signbit(d_a)]: entry n + 1 (d >= +0) or n (sign set)
   float o[3], bound, dt_gamma, halfH, hm1, t_lo, t_hi, dt_min, dt_max;   // pinned copies of per-frame constants
   uint32_t H;
   int cm1;
+  const uint32_t* occ;  // P.occupancy, pinned like the constants above
 };
 __device__ __forceinline__ void ray_ctx(const MarchParams& P, const float* lut, const float d[3], RayCtx& R) {
   const uint32_t base = (uint32_t)__cvta_generic_to_shared(lut);
@@ -101,6 +102,8 @@ __device__ __forceinline__ void ray_ctx(const MarchParams& P, const float* lut, 
   R.t_lo = lds_f32(cb + 28); R.t_hi = lds_f32(cb + 32);
   R.H = __float_as_uint(lds_f32(cb + 36)); R.cm1 = (int)__float_as_uint(lds_f32(cb + 40));
   R.dt_min = lds_f32(cb + 44); R.dt_max = lds_f32(cb + 48);
+  R.occ = reinterpret_cast<const uint32_t*>(((unsigned long long)__float_as_uint(lds_f32(cb + 56)) << 32) |
+                                            __float_as_uint(lds_f32(cb + 52)));
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
     R.d[a] = d[a];
@@ -128,7 +131,7 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
     mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
   }
   // mip_from_pos: frexpf exponent of the max-norm, clamped to [0, C-1]  (exact, done on the bit pattern)
-  const int e = (int)((__float_as_uint(mx) >> 23) & 0xffu) - 126;
+  const int e = (int)(__float_as_uint(mx) >> 23) - 126;  // mx >= 0: the sign bit is clear, no mask needed
   const int level = max(0, min(FAST ? R.cm1 : (int)P.C - 1, e));
   const float pow2 = __uint_as_float((uint32_t)(127 + level) << 23);
   const bool capped = !FAST && pow2 > P.bound;
@@ -149,7 +152,10 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
     nz = (int)clampf((z * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
   }
   const uint32_t cell = ((level * H + nx) * H + ny) * H + nz;
-  const bool occ = (__ldg(P.occupancy + (cell >> 5)) >> (cell & 31u)) & 1u;
+  uint32_t occ_u;  // ((word >> (cell & 31)) & 1) != 0, kept opaque: SHF + predicate-writing LOP3 (2 issue slots, not 3)
+  asm("{ .reg .pred p; .reg .b32 m; shr.b32 m, %1, %2; and.b32 m, m, 1; setp.ne.u32 p, m, 0; selp.u32 %0, 1, 0, p; }"
+      : "=r"(occ_u) : "r"(__ldg(R.occ + (cell >> 5))), "r"(cell & 31u));
+  const bool occ = occ_u != 0u;
   if (occ) {
     s.x = x; s.y = y; s.z = z;
     const float dt = clampf(t * R.dt_gamma, R.dt_min, R.dt_max);
@@ -171,7 +177,8 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
     tz = ((qz * 2.0f - 1.0f) * mip_bound - z) * R.rd[2];
   }
   const float tt = t + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
-  if (FAST && t >= R.t_lo && fmaxf(t, tt) <= R.t_hi) {
+  // tt >= t (the increment is max(0, .), and max(0, NaN) = 0), so every t the loop multiplies lies in [t, tt]
+  if (FAST && t >= R.t_lo && tt <= R.t_hi) {
     do { t = __fmaf_rn(t, R.dt_gamma, t); } while (t < tt);   // dt_min <= t*dt_gamma <= dt_max on every step taken
   } else {
     do {
@@ -191,6 +198,8 @@ __device__ __forceinline__ void load_lut(const MarchParams& P, float* lut) {
     c[0] = P.o[0]; c[1] = P.o[1]; c[2] = P.o[2]; c[3] = P.bound; c[4] = P.dt_gamma;
     c[5] = 0.5f * (float)P.H; c[6] = (float)(P.H - 1); c[7] = P.t_lo; c[8] = P.t_hi;
     c[9] = __uint_as_float(P.H); c[10] = __uint_as_float(P.C - 1u); c[11] = P.dt_min; c[12] = P.dt_max;
+    const unsigned long long op = (unsigned long long)P.occupancy;
+    c[13] = __uint_as_float((uint32_t)op); c[14] = __uint_as_float((uint32_t)(op >> 32));
   }
   __syncthreads();
 }
@@ -206,12 +215,12 @@ __device__ __forceinline__ int count_ray_t(const MarchParams& P, const RayCtx& R
   int c = 0;
   t_first = near;
   Step s;
-  while (t < far && c < NRF_MAX_STEPS_D) {
+  while (t < far) {  // the sample cap is tested where c changes, not on every empty step
     const float t0 = t;
     if (march_step<FAST>(P, R, t, s)) {
       if (c == 0) t_first = t0;
       if (tc && c < NRF_TCACHE) tc[32 * c] = t0;
-      ++c;
+      if (++c >= NRF_MAX_STEPS_D) break;
     }
   }
   return c;
