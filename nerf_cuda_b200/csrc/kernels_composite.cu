@@ -15,8 +15,8 @@
 
 extern "C" __global__ void __launch_bounds__(128)
 k_composite(int n_rays, ShardMap map, const int* __restrict__ warp_base, const int* __restrict__ counts,
-            const float4* __restrict__ rays, const float2* __restrict__ far_tf, const float4* __restrict__ samples,
-            const float* __restrict__ t_after, const uint2* __restrict__ sample_out, float* __restrict__ rgb_f32,
+            const float4* __restrict__ rays, const float2* __restrict__ far_tf, const __grid_constant__ SampleSrc S,
+            const uint2* __restrict__ sample_out, float* __restrict__ rgb_f32,
             float* __restrict__ depth_f32, int* __restrict__ used_counts, uint8_t* __restrict__ rgb_u8,
             uint8_t* __restrict__ depth_u8, int u8_pixel_order) {
   const int lane = threadIdx.x & 31;
@@ -55,9 +55,13 @@ k_composite(int n_rays, ShardMap map, const int* __restrict__ warp_base, const i
     for (int j = 0; j < COMP_CHUNK; ++j) {
       if (has[j] && running) {
         so[j] = __ldg(sample_out + idx[j]);
-        dts[j] = __ldg(&samples[idx[j]].w);
-        tas[j] = __ldg(t_after + idx[j]);
+        tas[j] = __ldg(S.t0 + idx[j]);   // the t the sample was taken at
       }
+    }
+#pragma unroll
+    for (int j = 0; j < COMP_CHUNK; ++j) {  // dt and t_after as the march step computed them (record_dt)
+      dts[j] = record_dt(S, tas[j]);
+      tas[j] += dts[j];
     }
 #pragma unroll
     for (int j = 0; j < COMP_CHUNK; ++j) {

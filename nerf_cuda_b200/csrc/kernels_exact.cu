@@ -136,7 +136,11 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
   const float pow2 = __uint_as_float((uint32_t)(127 + level) << 23);
   const bool capped = !FAST && pow2 > P.bound;
   const float mip_bound = capped ? P.bound : pow2;
-  const float mip_rbound = capped ? P.rbound : __uint_as_float((uint32_t)(127 - level) << 23);
+  // 2^-level from 2^level: the two bit patterns add up to 0x7f000000 — one IADD; kept opaque, or the compiler turns it
+  // back into a constant load + IMAD
+  uint32_t rb_bits;
+  asm("sub.u32 %0, 0x7f000000, %1;" : "=r"(rb_bits) : "r"(__float_as_uint(pow2)));
+  const float mip_rbound = capped ? P.rbound : __uint_as_float(rb_bits);
   const uint32_t H = FAST ? R.H : P.H;
   // reference: (int)clamp(0.5 /*double*/ * (x*rb+1) * H, 0, H-1).  0.5*H is exact in float and the double product is
   // exact, so one float multiply by (0.5f*H) rounds identically (DESIGN.md numerics contract).
@@ -361,7 +365,7 @@ k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ 
        const int* __restrict__ counts, const int* __restrict__ block_bases, int* __restrict__ warp_base,
        float4* __restrict__ samples, float* __restrict__ t_after, int* __restrict__ sample_ray,
        float* __restrict__ dbg, const long long* __restrict__ dbg_offsets, long long capacity,
-       const float* __restrict__ tcache) {
+       const float* __restrict__ tcache, float* __restrict__ t_rec) {
   __shared__ float lut[NRF_MAX_GRID + 1 + LUT_CONST];
   __shared__ int wsum[RAYS_BLOCK / 32];
   __shared__ uint32_t died[RAYS_BLOCK / 32][NRF_MAX_STEPS_D];
@@ -414,20 +418,31 @@ k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ 
       const float dt = clampf(t0 * R.dt_gamma, R.dt_min, R.dt_max);
       t = t0 + dt;
       const long long k = off + __popc(alive & lt);
-      samples[k] = make_float4(P.pos_w * x + 0.5f, P.pos_w * y + 0.5f, P.pos_w * z + 0.5f, dt);
-      t_after[k] = t;
-      sample_ray[k] = q;
+      if (t_rec) {   // frame path (SampleSrc): ray index in the fourth component, the sample's t beside it
+        samples[k] = make_float4(P.pos_w * x + 0.5f, P.pos_w * y + 0.5f, P.pos_w * z + 0.5f, __int_as_float(q));
+        t_rec[k] = t0;
+      } else {
+        samples[k] = make_float4(P.pos_w * x + 0.5f, P.pos_w * y + 0.5f, P.pos_w * z + 0.5f, dt);
+        t_after[k] = t;
+        sample_ray[k] = q;
+      }
       off += __popc(alive);
       alive &= ~died[warp][c];
       t0 = tn;
     }
   }
   while (t < far && c < c_total) {
+    const float t0 = t;
     if (!(fast ? march_step<true>(P, R, t, s) : march_step<false>(P, R, t, s))) continue;
     const long long k = off + __popc(alive & lt);
-    samples[k] = make_float4(P.pos_w * s.x + 0.5f, P.pos_w * s.y + 0.5f, P.pos_w * s.z + 0.5f, s.dt);
-    t_after[k] = t;
-    sample_ray[k] = q;
+    if (t_rec) {
+      samples[k] = make_float4(P.pos_w * s.x + 0.5f, P.pos_w * s.y + 0.5f, P.pos_w * s.z + 0.5f, __int_as_float(q));
+      t_rec[k] = t0;
+    } else {
+      samples[k] = make_float4(P.pos_w * s.x + 0.5f, P.pos_w * s.y + 0.5f, P.pos_w * s.z + 0.5f, s.dt);
+      t_after[k] = t;
+      sample_ray[k] = q;
+    }
     if (dbg) {
       float* o = dbg + (dbg0 + c) * 8;
       o[0] = s.x; o[1] = s.y; o[2] = s.z; o[3] = s.dt; o[4] = t;

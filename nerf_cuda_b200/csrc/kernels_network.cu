@@ -297,7 +297,7 @@ __global__ void __launch_bounds__(NET_GROUPS * 128, 1)
 k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__ samples,
           const int* __restrict__ sample_ray, const float4* __restrict__ rays, const uint4* __restrict__ ray_sh,
           int dirs_mode, uint4* __restrict__ enc_io, uint2* __restrict__ out, uint32_t* __restrict__ idx_out,
-          const unsigned long long* __restrict__ n_dev) {
+          const unsigned long long* __restrict__ n_dev, const __grid_constant__ SampleSrc S) {
   // frame path: the sample count is still in device memory when this kernel is enqueued (no host round trip in the
   // middle of a frame); `n` is then the capacity of the sample buffers
   // (a total above the capacity means the list has holes — k_emit skipped the patches that did not fit — and the host
@@ -413,7 +413,8 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     if (dirs_mode == 0) {
       uint4 a = make_uint4(0, 0, 0, 0), b = a;
       if (valid) {
-        const int ray = __ldg(sample_ray + i);
+        // frame path: the ray index rides in the sample record's fourth component (SampleSrc)
+        const int ray = S.t0 ? __float_as_int(__ldg(&samples[i].w)) : __ldg(sample_ray + i);
         a = __ldg(ray_sh + 2 * (size_t)ray);
         b = __ldg(ray_sh + 2 * (size_t)ray + 1);
       }
@@ -563,10 +564,12 @@ static void nrf_network_setup() {
 extern "C" cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t stream, const NetParams* P, int n,
                                           const float4* samples, const int* sample_ray, const float4* rays,
                                           const uint4* ray_sh, int dirs_mode, uint4* enc_io, uint2* out,
-                                          uint32_t* idx_out, const unsigned long long* n_dev) {
+                                          uint32_t* idx_out, const unsigned long long* n_dev, const SampleSrc* src) {
   nrf_network_setup();
+  SampleSrc S{};
+  if (src) S = *src;
   if (n <= 0) return cudaSuccess;
-#define NET_ARGS *P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out, n_dev
+#define NET_ARGS *P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out, n_dev, S
   switch (mode) {
     case 0: k_network<0, 8><<<grid, 1024, NET_SMEM, stream>>>(NET_ARGS); break;
     case 1: k_network<1, 8><<<grid, 1024, NET_SMEM, stream>>>(NET_ARGS); break;

@@ -36,7 +36,8 @@ __global__ void k_count_given(const MarchParams P, int n, const float4* rays, fl
 __global__ void k_scan_blocks(int* block_sums, int n_blocks, unsigned long long* total);
 __global__ void k_emit(const MarchParams P, int n, const float4* rays, const float2* far_tf, const int* counts,
                        const int* block_bases, int* warp_base, float4* samples, float* t_after, int* sample_ray,
-                       float* dbg, const long long* dbg_offsets, long long capacity, const float* tcache);
+                       float* dbg, const long long* dbg_offsets, long long capacity, const float* tcache,
+                       float* t_rec);
 __global__ void k_build_occupancy(const float* grid, uint32_t n_cells, float thresh, uint32_t* bits);
 __global__ void k_cast_half(const float* in, __half* out, size_t n);
 __global__ void k_accumulate(int n, const float4* frame, float4* accum, float sample_count, int color_space);
@@ -46,14 +47,14 @@ __global__ void k_dg_positions(uint32_t H, float bound_c, float half, float pos_
                                unsigned long long elem0, float4* samples);
 __global__ void k_dg_update(uint32_t n, const uint2* sample_out, float decay, int reset, float* grid, double* sum);
 __global__ void k_composite(int n_rays, ShardMap map, const int* warp_base, const int* counts, const float4* rays,
-                            const float2* far_tf, const float4* samples, const float* t_after, const uint2* sample_out,
+                            const float2* far_tf, const SampleSrc S, const uint2* sample_out,
                             float* rgb_f32, float* depth_f32, int* used_counts, uint8_t* rgb_u8, uint8_t* depth_u8,
                             int u8_pixel_order);
 size_t nrf_network_smem_bytes();
 cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t stream, const NetParams* P, int n,
                                const float4* samples, const int* sample_ray, const float4* rays, const uint4* ray_sh,
                                int dirs_mode, uint4* enc_io, uint2* out, uint32_t* idx_out,
-                               const unsigned long long* n_dev);
+                               const unsigned long long* n_dev, const SampleSrc* src);
 cudaError_t nrf_launch_encode_exp(int variant, int sms, cudaStream_t stream, const NetParams* P, int n,
                                   const float4* samples, uint4* enc_io);
 cudaError_t nrf_launch_network_simt(cudaStream_t stream, const NetParams* P, int n, const uint4* enc,
@@ -207,6 +208,7 @@ struct Device {
   DevBuf<float4> rays, samples;
   DevBuf<uint4> ray_sh;
   DevBuf<float2> far_tf;
+  DevBuf<float> t0rec;          // the t of every sample of the frame (SampleSrc)
   DevBuf<float> t_after, rgb_f32, depth_f32, tcache;
   DevBuf<int> counts, warp_base, block_sums, sample_ray, used;
   DevBuf<uint2> sample_out;
@@ -292,7 +294,7 @@ extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
 static void free_device(Device& D) {
   cudaSetDevice(D.dev);
   D.params_h.release(); D.mlp_packed.release(); D.occupancy.release(); D.density_grid.release(); D.div_lut.release();
-  D.rays.release(); D.ray_sh.release(); D.tcache.release(); D.samples.release(); D.far_tf.release(); D.t_after.release(); D.rgb_f32.release();
+  D.rays.release(); D.ray_sh.release(); D.tcache.release(); D.t0rec.release(); D.samples.release(); D.far_tf.release(); D.t_after.release(); D.rgb_f32.release();
   D.depth_f32.release(); D.counts.release(); D.warp_base.release(); D.block_sums.release();
   D.sample_ray.release(); D.used.release(); D.sample_out.release(); D.rgb_u8.release(); D.depth_u8.release();
   D.total.release(); D.enc.release(); D.idx.release(); D.dbg.release();
@@ -624,15 +626,23 @@ static inline uint8_t* peer_slot_ptr(nrf_ctx* c) { return c->peer_frame + (size_
 // memory, k_emit / k_network / k_composite read it there; the sample buffers keep the capacity of earlier frames.
 // If the total exceeds the capacity the overflowing patches are skipped on the device (k_emit marks them) and
 // frame_check() — at the next host sync — grows the buffers and asks for the frame to be rendered again.
+static SampleSrc sample_src(const Device& D) {
+  SampleSrc s{};
+  s.t0 = D.t0rec.p;
+  s.dt_gamma = D.march.dt_gamma; s.dt_min = D.march.dt_min; s.dt_max = D.march.dt_max;
+  return s;
+}
+
 static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float* pose) {
   CU(cudaSetDevice(D.dev));
   set_pose(c, D.march, intr, pose);
   const int nb = (D.n_local + 127) / 128;
-  if (D.samples.n == 0) {  // first frame at this resolution: start from 32 samples per ray
+  if (D.t0rec.n == 0) {  // first frame at this resolution: start from 32 samples per ray
     const size_t want = std::max<size_t>((size_t)D.n_local * 32, 4096);
-    CU(D.samples.ensure(want)); CU(D.t_after.ensure(want)); CU(D.sample_ray.ensure(want)); CU(D.sample_out.ensure(want));
+    CU(D.samples.ensure(want)); CU(D.t0rec.ensure(want)); CU(D.sample_out.ensure(want));
   }
-  const size_t cap = std::min<size_t>(D.samples.n, (1ull << 31) - 256);
+  const size_t cap = std::min<size_t>(std::min(D.samples.n, std::min(D.t0rec.n, D.sample_out.n)), (1ull << 31) - 256);
+  const SampleSrc src = sample_src(D);
   CU(cudaEventRecord(D.ev[0], D.stream));
   if (D.n_local > 0) {
     k_rays_count<<<nb, 128, 0, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
@@ -646,18 +656,18 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
   CU(cudaMemcpyAsync(D.total_h + (D.frame_no & 3u), D.total.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, D.stream));
   if (D.n_local > 0) {
     k_emit<<<nb, 128, 0, D.stream>>>(D.march, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
-                                    D.warp_base.p, D.samples.p, D.t_after.p, D.sample_ray.p, nullptr, nullptr,
-                                    (long long)cap, D.tcache.p);
+                                    D.warp_base.p, D.samples.p, nullptr, nullptr, nullptr, nullptr,
+                                    (long long)cap, D.tcache.p, D.t0rec.p);
     CU(cudaGetLastError());
   }
   CU(cudaEventRecord(D.ev[2], D.stream));
-  CU(nrf_launch_network(2, network_grid(c, D, (int)cap), D.stream, &D.net, (int)cap, D.samples.p, D.sample_ray.p, D.rays.p,
-                        D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr, D.total.p));
+  CU(nrf_launch_network(2, network_grid(c, D, (int)cap), D.stream, &D.net, (int)cap, D.samples.p, nullptr, D.rays.p,
+                        D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr, D.total.p, &src));
   CU(cudaEventRecord(D.ev[3], D.stream));
   if (D.n_local > 0) {
     Device& D0 = c->devs[0];
-    k_composite<<<nb, 128, 0, D.stream>>>(D.n_local, D.map, D.warp_base.p, D.counts.p, D.rays.p, D.far_tf.p, D.samples.p,
-                                          D.t_after.p, D.sample_out.p, D.rgb_f32.p, D.depth_f32.p, D.used.p,
+    k_composite<<<nb, 128, 0, D.stream>>>(D.n_local, D.map, D.warp_base.p, D.counts.p, D.rays.p, D.far_tf.p, src,
+                                          D.sample_out.p, D.rgb_f32.p, D.depth_f32.p, D.used.p,
                                           c->peer_frame ? peer_slot_ptr(c) : D0.rgb_u8.p,
                                           c->peer_frame ? peer_slot_ptr(c) + (size_t)c->W * c->H * 3 : D0.depth_u8.p,
                                           (c->n_shards == 1 || c->peer_frame) ? 1 : 0);
@@ -680,10 +690,10 @@ static int frame_check(nrf_ctx*, Device& D, bool& redo) {
   D.total_h[D.frame_no & 3u] = S;
   if (mx > (1ull << 31) - 256) return fail(NRF_EINVAL, "frame produces %llu samples (> 2^31)", mx);
   D.last_samples = S;
-  const size_t cap = D.samples.n;
+  const size_t cap = std::min(D.samples.n, std::min(D.t0rec.n, D.sample_out.n));
   if (mx > cap) {
     const size_t want = (size_t)mx + (size_t)mx / 4;
-    CU(D.samples.ensure(want)); CU(D.t_after.ensure(want)); CU(D.sample_ray.ensure(want)); CU(D.sample_out.ensure(want));
+    CU(D.samples.ensure(want)); CU(D.t0rec.ensure(want)); CU(D.sample_out.ensure(want));
   }
   if (S > cap) redo = true;
   return NRF_OK;
@@ -955,7 +965,7 @@ extern "C" int nrf_probe_march(nrf_ctx* c, int n, const float rays_o[3], const f
       CU(doff.ensure(n));
       CU(cudaMemcpyAsync(doff.p, ho.data(), (size_t)n * 8, cudaMemcpyHostToDevice, D.stream));
       CU(smp.ensure(S)); CU(ta.ensure(S)); CU(sray.ensure(S)); CU(dbg.ensure(S * 8));
-      k_emit<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p, wb.p, smp.p, ta.p, sray.p, dbg.p, doff.p, (long long)S, nullptr);
+      k_emit<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p, wb.p, smp.p, ta.p, sray.p, dbg.p, doff.p, (long long)S, nullptr, nullptr);
       CU(cudaGetLastError());
       CU(cudaMemcpyAsync(samples, dbg.p, (size_t)S * 32, cudaMemcpyDeviceToHost, D.stream));
       CU(cudaStreamSynchronize(D.stream));
@@ -998,7 +1008,7 @@ extern "C" int nrf_probe_encode(nrf_ctx* c, int n, const float* positions, uint1
   CU(D.enc.ensure((size_t)n * 4));
   if (indices_out) CU(D.idx.ensure((size_t)n * NRF_L * 8));
   CU(nrf_launch_network(0, network_grid(c, D, n), D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p,
-                        nullptr, indices_out ? D.idx.p : nullptr, nullptr));
+                        nullptr, indices_out ? D.idx.p : nullptr, nullptr, nullptr));
   CU(cudaMemcpyAsync(enc_out, D.enc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, D.stream));
   if (indices_out) CU(cudaMemcpyAsync(indices_out, D.idx.p, (size_t)n * NRF_L * 8 * 4, cudaMemcpyDeviceToHost, D.stream));
   CU(cudaStreamSynchronize(D.stream));
@@ -1017,7 +1027,7 @@ extern "C" int nrf_probe_network(nrf_ctx* c, int n, const uint16_t* enc, const f
   CU(D.enc.ensure((size_t)n * 4)); CU(o.ensure(n));
   CU(cudaMemcpyAsync(D.enc.p, enc, (size_t)n * 64, cudaMemcpyHostToDevice, D.stream));
   if (impl == 1) CU(nrf_launch_network_simt(D.stream, &D.net, n, D.enc.p, d4.p, o.p));
-  else CU(nrf_launch_network(1, network_grid(c, D, n), D.stream, &D.net, n, nullptr, nullptr, d4.p, nullptr, 1, D.enc.p, o.p, nullptr, nullptr));
+  else CU(nrf_launch_network(1, network_grid(c, D, n), D.stream, &D.net, n, nullptr, nullptr, d4.p, nullptr, 1, D.enc.p, o.p, nullptr, nullptr, nullptr));
   std::vector<uint2> h(n);
   CU(cudaMemcpyAsync(h.data(), o.p, (size_t)n * 8, cudaMemcpyDeviceToHost, D.stream));
   CU(cudaStreamSynchronize(D.stream));
@@ -1036,7 +1046,7 @@ extern "C" int nrf_probe_samples(nrf_ctx* c, int n, const float* positions, cons
   if (!rc) rc = upload_vec3_as_float4(D, n, dirs, d4);
   if (rc) return rc;
   CU(o.ensure(n));
-  CU(nrf_launch_network(2, network_grid(c, D, n), D.stream, &D.net, n, p4.p, nullptr, d4.p, nullptr, 1, nullptr, o.p, nullptr, nullptr));
+  CU(nrf_launch_network(2, network_grid(c, D, n), D.stream, &D.net, n, p4.p, nullptr, d4.p, nullptr, 1, nullptr, o.p, nullptr, nullptr, nullptr));
   std::vector<uint2> h(n);
   CU(cudaMemcpyAsync(h.data(), o.p, (size_t)n * 8, cudaMemcpyDeviceToHost, D.stream));
   CU(cudaStreamSynchronize(D.stream));
@@ -1059,14 +1069,15 @@ extern "C" int nrf_bench_stage(nrf_ctx* c, int what, int n, int iters, float* ms
   if (S <= 0) return fail(NRF_ESTATE, "render a frame first (the stage bench replays its samples)");
   CU(D.enc.ensure((size_t)S * 4));
   const int grid = network_grid(c, D, S);
+  const SampleSrc src = sample_src(D);
   if (what == 1)  // produce the features once
-    CU(nrf_launch_network(0, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, nullptr, nullptr, nullptr));
+    CU(nrf_launch_network(0, grid, D.stream, &D.net, S, D.samples.p, nullptr, D.rays.p, D.ray_sh.p, 0, D.enc.p, nullptr, nullptr, nullptr, &src));
   cudaEvent_t e0, e1;
   CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
-  CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, D.sample_out.p, nullptr, nullptr));
+  CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, nullptr, D.rays.p, D.ray_sh.p, 0, D.enc.p, D.sample_out.p, nullptr, nullptr, &src));
   CU(cudaEventRecord(e0, D.stream));
   for (int i = 0; i < iters; ++i)
-    CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, D.sample_ray.p, D.rays.p, D.ray_sh.p, 0, D.enc.p, D.sample_out.p, nullptr, nullptr));
+    CU(nrf_launch_network(what, grid, D.stream, &D.net, S, D.samples.p, nullptr, D.rays.p, D.ray_sh.p, 0, D.enc.p, D.sample_out.p, nullptr, nullptr, &src));
   CU(cudaEventRecord(e1, D.stream));
   CU(cudaEventSynchronize(e1));
   float ms = 0;
@@ -1088,10 +1099,10 @@ extern "C" int nrf_bench_encode_positions(nrf_ctx* c, int n, const float* positi
   const int grid = network_grid(c, D, n);
   cudaEvent_t e0, e1;
   CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
-  CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr, nullptr));
+  CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr, nullptr, nullptr));
   CU(cudaEventRecord(e0, D.stream));
   for (int i = 0; i < iters; ++i)
-    CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr, nullptr));
+    CU(nrf_launch_network(0, grid, D.stream, &D.net, n, pos.p, nullptr, nullptr, nullptr, 1, D.enc.p, nullptr, nullptr, nullptr, nullptr));
   CU(cudaEventRecord(e1, D.stream));
   CU(cudaEventSynchronize(e1));
   float ms = 0;
@@ -1191,7 +1202,7 @@ extern "C" int nrf_generate_density_grid(nrf_ctx* c, float decay, int reset, uns
                                                            3ull * cas * H3, D.samples.p);
       CU(cudaGetLastError());
       CU(nrf_launch_network(2, network_grid(c, D, (int)H3), D.stream, &D.net, (int)H3, D.samples.p, D.sample_ray.p,
-                            D.rays.p, D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr, nullptr));
+                            D.rays.p, D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr, nullptr, nullptr));
       k_dg_update<<<(H3 + 255) / 256, 256, 0, D.stream>>>(H3, D.sample_out.p, decay, reset,
                                                         D.density_grid.p + (size_t)cas * H3, sum.p);
       CU(cudaGetLastError());

@@ -8,8 +8,9 @@
 //   occupancy  : uint32[C*H^3/32]         bit == (density > min(0.01, mean_density)), same linear cell index as
 //                                         the reference's float grid (render_utils.h:613-619)
 //   rays       : float4[N] {dx,dy,dz,near} + float2[N] {far, t_first}; N = local rays in patch-major order (ShardMap)
-//   samples    : float4[S] {u,v,w (position normalised to [0,1]), dt} + float[S] t_after + int[S] ray, in
+//   samples    : float4[S] {u,v,w (position normalised to [0,1]), ray index} + float[S] t (SampleSrc), in
 //                WARP-INTERLEAVED order: for each 32-ray patch, step k of all its live rays, then step k+1, ...
+//                (stage probes: float4 {u,v,w,dt} + float[S] t_after + int[S] ray)
 //   warp_base  : int[N/32] first sample of each patch
 //   tcache     : float[N/32][NRF_TCACHE][32] t of each ray's first NRF_TCACHE samples (pass 1 -> pass 2)
 //   ray_sh     : uint4[2N] the 16 fp16 SH coefficients of every ray's direction
@@ -58,6 +59,15 @@ struct MarchParams {
   float t_lo, t_hi;      // dt_min/dt_gamma, dt_max/dt_gamma: between them t*dt_gamma needs no clamp
 };
 
+// Frame path: a sample is the 16-byte record {u,v,w, ray index} k_network reads, plus the t it was taken at (4 B) for
+// k_composite: dt and t_after are functions of t and the per-frame constants below and are recomputed there with
+// exactly the expressions of the march step (20 B per sample written instead of 24, and the composite reads 12 B per
+// sample in whole sectors instead of 28 B in quarter-used ones).
+struct SampleSrc {
+  const float* t0;     // null: explicit arrays instead (stage probes, density grid): samples[i].w = dt, sample_ray[i]
+  float dt_gamma, dt_min, dt_max;
+};
+
 // activation ids mirror include/nerf_b200.h
 #define ACT_NONE 0
 #define ACT_RELU 1
@@ -65,6 +75,10 @@ struct MarchParams {
 #define ACT_SIGMOID 3
 
 #ifdef __CUDACC__
+// dt of the occupied branch of the march step (kernels_exact.cu march_step) at a recorded t
+__device__ __forceinline__ float record_dt(const SampleSrc& S, float t) {
+  return fminf(S.dt_max, fmaxf(S.dt_min, t * S.dt_gamma));
+}
 __device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
   return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
 }
