@@ -15,6 +15,10 @@
 #include "nrf_device.cuh"
 
 #define RAYS_BLOCK 128
+#define RAYS_MIN_BLOCKS 8
+#ifndef COUNT_MIN_BLOCKS
+#define COUNT_MIN_BLOCKS 8   // k_rays_count: 47 registers = 10 resident blocks; asking for 10 or 12 measured 3 % / 14 % slower
+#endif
 #define NRF_MAX_GRID 512  // largest density_grid_size (check_arch)
 
 __device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(hi, fmaxf(lo, x)); }
@@ -260,7 +264,7 @@ __device__ __forceinline__ void block_total(int c, int* __restrict__ block_sums)
 
 // Pass 1: rays of this shard (patch-major order, ShardMap) + sample counts + per-block totals.
 // rays: float4 {dx,dy,dz,near}; far_tf: float2 {far, t_first}; counts; block_sums[gridDim.x]
-extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, 8)
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, COUNT_MIN_BLOCKS)
 k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, float4* __restrict__ rays,
              float2* __restrict__ far_tf, int* __restrict__ counts, int* __restrict__ block_sums,
              uint4* __restrict__ ray_sh, float* __restrict__ tcache) {
@@ -304,7 +308,7 @@ k_rays_given_pixels(const __grid_constant__ MarchParams P, int pix0, int n, floa
 }
 
 // Count-only variant for externally supplied rays (stage probe nrf_probe_march).
-extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, 8)
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, RAYS_MIN_BLOCKS)
 k_count_given(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays,
               float2* __restrict__ far_tf, int* __restrict__ counts, int* __restrict__ block_sums) {
   __shared__ float lut[NRF_MAX_GRID + 1 + LUT_CONST];
@@ -360,7 +364,7 @@ extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict
 // march in lockstep.  warp_base[] (first sample of every warp) is kept for the composite kernel.
 // samples: float4 {u,v,w,dt} (position already normalised: x*pos_w+0.5, nerf_render.cu:311-312), t_after, ray id.
 // dbg (optional, probe only): per sample {x,y,z,dt,t_after,level,cell,ray} raw, RAY-major at dbg_offsets[q] + k.
-extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, 8)
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, RAYS_MIN_BLOCKS)
 k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays, const float2* __restrict__ far_tf,
        const int* __restrict__ counts, const int* __restrict__ block_bases, int* __restrict__ warp_base,
        float4* __restrict__ samples, float* __restrict__ t_after, int* __restrict__ sample_ray,

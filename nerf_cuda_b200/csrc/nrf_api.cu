@@ -645,7 +645,9 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
   const SampleSrc src = sample_src(D);
   CU(cudaEventRecord(D.ev[0], D.stream));
   if (D.n_local > 0) {
-    k_rays_count<<<nb, 128, 0, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
+    // experiment knob: unused dynamic shared memory caps the resident blocks per SM (registers allow 10)
+    static const int count_dyn_smem = std::getenv("NRF_COUNT_DYN_SMEM") ? std::atoi(std::getenv("NRF_COUNT_DYN_SMEM")) : 0;
+    k_rays_count<<<nb, 128, count_dyn_smem, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
                                           D.ray_sh.p, D.tcache.p);
     CU(cudaGetLastError());
   }
