@@ -241,8 +241,15 @@ def gpu_arm(args):
         sampler.start()
     for i in range(len(poses)):          # size every buffer for the largest pose before anything is timed
         frame(i, False)
+    r.synchronize()                      # sync point: the buffers grow to the largest frame enqueued so far
+    ovf0 = r.overflowed_frames()
     ms_dev, _, _ = timed(False, args.steps, args.warmup)
     ms_e2e, net_ms, samples = timed(True, args.steps, max(3, args.warmup // 2), collect_stats=True)
+    # frames are enqueued without host syncs: one that did not fit the sample buffers would have been rendered
+    # incompletely (and too fast) — none may have occurred inside the timed regions
+    ovf = r.overflowed_frames() - ovf0
+    if ovf:
+        raise RuntimeError(f"{ovf} timed frame(s) overflowed the sample buffers: the measurement is invalid")
     batch_rps = None
     if world == 1:   # the same host-in / host-out work through the pipelined batch call (render_server --batch)
         pb = np.stack([poses[(args.warmup + i) % len(poses)] for i in range(args.steps)])
@@ -284,12 +291,13 @@ def gpu_arm(args):
                            f"rank 0's frame over NVLink (CUDA IPC peer stores), 4-byte NCCL all-reduce as completion fence" if peer else
                            f"32x32-pixel tiles round-robin over {world} ranks, NCCL gather of packed u8 tiles to rank 0"),
                        "samples_per_frame": smp_total, "samples_per_ray": smp_total / rays,
-                       "l2": f"inputs larger than L2: each frame streams {smp_total / world * 60 / 1e6:.0f} MB of sample records per GPU "
+                       "l2": f"inputs larger than L2: each frame streams {smp_total / world * 56 / 1e6:.0f} MB of sample records per GPU (20 B written by the march, 16 read + 8 written by the network, 12 read by the composite) "
                              f"and the pose changes every step; the {table_mb:.1f} MB hash table is "
                              + ("L2-resident by design" if table_mb < 100 else "far larger than the 126 MB L2 (HBM-resident gather)")},
             "e2e": {"value": rays * args.steps / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
                     "batch_call_value": batch_rps, "h2d_bytes_per_step": 80, "d2h_bytes_per_step": rays * 4 + 8 if (world == 1 or peer) else rays * 3 + 8},
             "gpu_launches": 5 * args.steps,
+            "overflowed_timed_frames": int(ovf),
             "clocks": clocks,
             "roofline": {"kernel": "k_network<2> (hash-grid gather + tcgen05 MLP, fused)", "bound": "hbm",
                          "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s", "frac": achieved / pk["hbm"],

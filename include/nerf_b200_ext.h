@@ -48,6 +48,13 @@ int nrf_peer_frame_detach(nrf_ctx* ctx);
 int nrf_peer_frame_device(nrf_ctx* ctx, void** frame);
 int nrf_peer_frame_to_host(nrf_ctx* ctx, uint8_t** rgb, uint8_t** depth);
 
+/* Asynchronous device frames (nrf_render_frame_device without a sync in between) whose samples did not fit the sample
+ * buffers: such a frame is rendered incompletely; the LATEST one is re-rendered at the next sync point, earlier ones
+ * are not (their pixels were already overwritten), and the buffers grow to the largest frame seen.  Cumulative count
+ * since nrf_set_resolution; a caller that times or keeps asynchronous frames checks that it did not move.  The
+ * reference has no equivalent: it blocks on a device->host read after every <= 8 march steps (nerf_render.cu:291). */
+int nrf_overflowed_frames(nrf_ctx* ctx, uint64_t* n_frames);
+
 /* Memory micro-benchmarks on device 0 (roofline denominators for the hash gather).  mode 0: coalesced
  * 16-byte streaming reads over a window (window <= L2 size => L2->SM bandwidth, window >> L2 => HBM read bandwidth);
  * mode 1: one random 8-byte slot per lane (one 32-byte sector in its own 128-byte line: the access shape of a hashed

@@ -239,6 +239,12 @@ class NerfRender:
                                        tonemap_curve, int(bool(clamp)), _p(out, C.c_float)))
         return accum, out
 
+    def overflowed_frames(self) -> int:
+        """Asynchronous frames that did not fit the sample buffers so far (nerf_b200_ext.h nrf_overflowed_frames)."""
+        n = C.c_uint64(0)
+        _check(self._l.nrf_overflowed_frames(self._ctx, C.byref(n)))
+        return int(n.value)
+
     def bench_memory(self, mode, window_bytes, iters=3):
         """Memory micro-benchmark (nerf_b200_ext.h nrf_bench_memory): returns (GB/s requested, loads per ns)."""
         g, l = C.c_float(), C.c_float()

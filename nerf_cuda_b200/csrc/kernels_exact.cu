@@ -327,8 +327,11 @@ k_count_given(const __grid_constant__ MarchParams P, int n, const float4* __rest
 }
 
 // One-block exclusive scan of the per-block totals (in place); total[0] = sum.  n_blocks <= 1024*64.
+// total[0] = samples of this frame; total[1] = running maximum over the frames since the host last looked (buffer growth:
+// frames are enqueued without host syncs); total[2] = number of frames whose samples did not fit `capacity`.
 extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict__ block_sums, int n_blocks,
-                                                                 unsigned long long* __restrict__ total) {
+                                                                 unsigned long long* __restrict__ total,
+                                                                 unsigned long long capacity) {
   __shared__ int wsum[32];
   __shared__ int carry_s;
   if (threadIdx.x == 0) carry_s = 0;
@@ -352,7 +355,12 @@ extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict
     if (threadIdx.x == 1023) carry_s = excl + v;
     __syncthreads();
   }
-  if (threadIdx.x == 0) total[0] = (unsigned long long)carry_s;
+  if (threadIdx.x == 0) {
+    const unsigned long long s = (unsigned long long)carry_s;
+    total[0] = s;
+    if (s > total[1]) total[1] = s;
+    if (s > capacity) total[2] += 1ull;
+  }
 }
 
 // Pass 2: re-march (from t_first) and emit the compact sample list in WARP-INTERLEAVED order: the samples of one warp

@@ -33,7 +33,7 @@ __global__ void k_rays_count(const MarchParams P, ShardMap map, int n_local, flo
 __global__ void k_rays_given_pixels(const MarchParams P, int pix0, int n, float4* rays, float* fars);
 __global__ void k_count_given(const MarchParams P, int n, const float4* rays, float2* far_tf, int* counts,
                               int* block_sums);
-__global__ void k_scan_blocks(int* block_sums, int n_blocks, unsigned long long* total);
+__global__ void k_scan_blocks(int* block_sums, int n_blocks, unsigned long long* total, unsigned long long capacity);
 __global__ void k_emit(const MarchParams P, int n, const float4* rays, const float2* far_tf, const int* counts,
                        const int* block_bases, int* warp_base, float4* samples, float* t_after, int* sample_ray,
                        float* dbg, const long long* dbg_offsets, long long capacity, const float* tcache,
@@ -220,7 +220,9 @@ struct Device {
   DevBuf<uint32_t> idx;
   DevBuf<float> dbg;
   unsigned long long last_samples = 0;
-  unsigned frame_no = 0;          // frames enqueued; the total of frame f lands in total_h[f & 3]
+  unsigned frame_no = 0;          // frames enqueued; {total, running max, overflowed frames} of frame f land in
+                                  // total_h[4 * (f & 3)] (k_scan_blocks)
+  unsigned long long overflowed = 0;  // frames that did not fit the sample buffers (as of the last sync point)
 };
 
 struct nrf_ctx {
@@ -273,8 +275,8 @@ extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&D.stream, cudaStreamNonBlocking);
     for (int k = 0; k < 6 && e == cudaSuccess; ++k) e = cudaEventCreate(&D.ev[k]);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&D.done, cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaMallocHost(&D.total_h, 4 * sizeof(unsigned long long));
-    if (e == cudaSuccess) std::memset(D.total_h, 0, 4 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMallocHost(&D.total_h, 16 * sizeof(unsigned long long));
+    if (e == cudaSuccess) std::memset(D.total_h, 0, 16 * sizeof(unsigned long long));
     cudaDeviceProp prop;
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, D.dev);
     if (e != cudaSuccess) {
@@ -540,6 +542,7 @@ extern "C" int nrf_set_resolution(nrf_ctx* c, int W, int H) {
     CU(D.rays.ensure(N)); CU(D.ray_sh.ensure(2 * N)); CU(D.far_tf.ensure(N)); CU(D.counts.ensure(N)); CU(D.warp_base.ensure((N + 31) / 32));
     CU(D.block_sums.ensure(nb)); CU(D.used.ensure(N)); CU(D.rgb_f32.ensure(N * 3)); CU(D.depth_f32.ensure(N));
     CU(D.total.ensure(4));
+    CU(cudaMemsetAsync(D.total.p, 0, 4 * sizeof(unsigned long long), D.stream));
     if (c->use_tcache) CU(D.tcache.ensure(((N + 31) / 32) * 32 * NRF_TCACHE));
     // u8 outputs: whole-frame contexts keep ONE frame in pixel order on device 0; a sharded context keeps its packed tiles
     if (g == 0) {
@@ -651,11 +654,11 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
                                           D.ray_sh.p, D.tcache.p);
     CU(cudaGetLastError());
   }
-  k_scan_blocks<<<1, 1024, 0, D.stream>>>(D.block_sums.p, D.n_local > 0 ? nb : 0, D.total.p);
+  k_scan_blocks<<<1, 1024, 0, D.stream>>>(D.block_sums.p, D.n_local > 0 ? nb : 0, D.total.p, (unsigned long long)cap);
   CU(cudaGetLastError());
   CU(cudaEventRecord(D.ev[1], D.stream));
   ++D.frame_no;
-  CU(cudaMemcpyAsync(D.total_h + (D.frame_no & 3u), D.total.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaMemcpyAsync(D.total_h + 4 * (D.frame_no & 3u), D.total.p, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, D.stream));
   if (D.n_local > 0) {
     k_emit<<<nb, 128, 0, D.stream>>>(D.march, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
                                     D.warp_base.p, D.samples.p, nullptr, nullptr, nullptr, nullptr,
@@ -681,15 +684,15 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
 }
 
 // After the device's stream has been synchronised: validates the LATEST frame's sample total (redo = it overflowed the
-// buffers and must be rendered again) and grows the buffers to the largest total any recent frame reported (frames
-// may be enqueued back to back without a host sync; only the latest one's result is still observable, the older
-// totals — a ring of four — are growth hints).
+// buffers and must be rendered again) and grows the buffers to the largest total of ANY frame enqueued since the last
+// check (a running maximum kept on the device: frames may be enqueued back to back without a host sync; only the
+// latest one's result is still observable, earlier frames that overflowed are counted — nrf_overflowed_frames).
 static int frame_check(nrf_ctx*, Device& D, bool& redo) {
   CU(cudaSetDevice(D.dev));
-  const unsigned long long S = D.total_h[D.frame_no & 3u];
-  unsigned long long mx = 0;
-  for (int k = 0; k < 4; ++k) { mx = std::max(mx, D.total_h[k]); D.total_h[k] = 0; }
-  D.total_h[D.frame_no & 3u] = S;
+  const unsigned long long* slot = D.total_h + 4 * (D.frame_no & 3u);
+  const unsigned long long S = slot[0], mx = slot[1];   // latest frame; largest frame since the last check
+  D.overflowed = slot[2];
+  CU(cudaMemsetAsync(D.total.p + 1, 0, sizeof(unsigned long long), D.stream));   // restart the running maximum
   if (mx > (1ull << 31) - 256) return fail(NRF_EINVAL, "frame produces %llu samples (> 2^31)", mx);
   D.last_samples = S;
   const size_t cap = std::min(D.samples.n, std::min(D.t0rec.n, D.sample_out.n));
@@ -806,7 +809,7 @@ extern "C" int nrf_render_batch(nrf_ctx* c, const float intr[4], const float* po
     const int slot = j & 1;
     CU(cudaEventSynchronize(c->batch_ev[slot]));
     bool over = false;
-    for (size_t g = 0; g < c->devs.size(); ++g) over |= c->devs[g].total_h[fno[slot][g] & 3u] > c->devs[g].samples.n;
+    for (size_t g = 0; g < c->devs.size(); ++g) over |= c->devs[g].total_h[4 * (fno[slot][g] & 3u)] > c->devs[g].samples.n;
     if (over) redo.push_back(j);
     else std::memcpy(rgb_out + (size_t)j * frame_bytes, c->batch_stage[slot], frame_bytes);
     return NRF_OK;
@@ -894,6 +897,15 @@ extern "C" int nrf_get_stats(nrf_ctx* c, nrf_stats* out) {
   return NRF_OK;
 }
 
+extern "C" int nrf_overflowed_frames(nrf_ctx* c, uint64_t* out) {
+  if (!c || !out) return fail(NRF_EINVAL, "null argument");
+  { int rc = frame_resolve(c); if (rc) return rc; }
+  uint64_t n = 0;
+  for (Device& D : c->devs) n += D.overflowed;
+  *out = n;
+  return NRF_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------- stage probes
 #define NEED_MODEL(c)                                                        \
   do {                                                                       \
@@ -950,7 +962,7 @@ extern "C" int nrf_probe_march(nrf_ctx* c, int n, const float rays_o[3], const f
   CU(cudaMemcpyAsync(f.p, hf.data(), (size_t)n * 8, cudaMemcpyHostToDevice, D.stream));
   k_count_given<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p);
   CU(cudaGetLastError());
-  k_scan_blocks<<<1, 1024, 0, D.stream>>>(bs.p, nb, tot.p);
+  k_scan_blocks<<<1, 1024, 0, D.stream>>>(bs.p, nb, tot.p, ~0ull);
   CU(cudaGetLastError());
   unsigned long long S = 0;
   CU(cudaMemcpyAsync(&S, tot.p, 8, cudaMemcpyDeviceToHost, D.stream));

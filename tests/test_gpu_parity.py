@@ -485,3 +485,39 @@ def test_sample_t_cache_replay_and_resume(pair, monkeypatch):
     O2 = orc.Oracle(sc.desc, sc.params, grid, sc.aabb)
     rgb2, dep2, cnt2 = O2.render(intr, pose, W, H)
     assert np.array_equal(a[3], cnt2) and np.abs(a[1] - rgb2).max() <= IMG_TOL
+
+
+def test_async_frames_growth_covers_every_enqueued_frame(pair):
+    """Frames enqueued back to back without a sync: the buffers must grow to the LARGEST of them at the next sync
+    point (a running maximum kept on the device), not to the latest few — a big frame followed by several small
+    ones must fit when it comes again — and frames that did not fit are counted (nrf_overflowed_frames).  Every cell
+    is occupied here, so a frame from the normal camera has hundreds of samples per ray (far more than the 32 per ray
+    a fresh context starts with) and one from very far away only a few pixels' worth."""
+    name, sc, r, O = pair
+    W, H = 64, 48
+    intr = syn.intrinsics(W, H)
+    pose = syn.look_at_pose(syn.camera_radius(name), 20.0, 15.0)
+    far_away = syn.look_at_pose(syn.camera_radius(name) * 40.0, 20.0, 15.0)
+    grid = np.ones_like(sc.grid)
+    rs = []
+    for _ in range(2):
+        x = NerfRender(1)
+        x.load_raw(sc.desc, sc.params, grid, sc.aabb)
+        x.set_resolution((W, H))
+        rs.append(x)
+    r2, r3 = rs
+    big = r3.render_frame(intr, pose)[0].copy()         # synchronous reference
+    assert r2.overflowed_frames() == 0
+    r2.render_frame_device(intr, pose)                  # overflows the initial buffers
+    for _ in range(6):
+        r2.render_frame_device(intr, far_away)          # six small frames push it out of any short history
+    r2.synchronize()                                    # growth to the running maximum happens here
+    n_ovf = r2.overflowed_frames()
+    assert n_ovf >= 1
+    r2.render_frame_device(intr, pose)                  # fits now: no new overflow, nothing to re-render
+    r2.render_frame_device(intr, far_away)
+    r2.synchronize()
+    assert r2.overflowed_frames() == n_ovf
+    assert np.array_equal(r2.render_frame(intr, pose)[0], big)
+    r2.close()
+    r3.close()
