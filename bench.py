@@ -34,7 +34,7 @@ WORKLOADS = {
     "C5": ("C5", 800, 800, 64),
 }
 GATHER_BYTES_PER_SAMPLE = 512      # 16 levels x 8 corners x 2 features x 2 B  
-STREAM_BYTES_PER_SAMPLE = 24 + 8   # sample record read (float4 + ray id + t_after) + {r,g,b,sigma} write
+STREAM_BYTES_PER_SAMPLE = 16 + 8   # sample record read (float4 {u,v,w, ray id}) + {r,g,b,sigma} write
 MLP_FLOP_PER_SAMPLE = 20480
 
 
@@ -262,7 +262,8 @@ def gpu_arm(args):
     stage = {}
     if rank == 0 or world == 1:
         stage = {k: r.bench_stage(w, 0, 3) for k, w in (("encode_ms", 0), ("mlp_ms", 1), ("fused_ms", 2))}
-    smp_local = samples[-1] if samples else 0
+    # the samples the stage bench replayed: those of the frame rendered LAST (after the batch call that is its last pose)
+    smp_local = int(r.stats().n_samples) if world == 1 else (samples[-1] if samples else 0)
     if world > 1:
         t = torch.tensor([float(np.mean(samples))], device="cuda", dtype=torch.float64)
         dist.all_reduce(t)
