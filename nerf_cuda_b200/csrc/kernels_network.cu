@@ -251,13 +251,23 @@ __device__ __forceinline__ void ld_relu_pack32(uint32_t taddr, uint32_t* packed)
 // threads gather 3-4 levels of tile j+8 (the group's next tile).  The gather slices sit in the five MMA waits where no
 // activation registers are live (after L0-lo, L1, V0-lo, V1-lo, V2 were issued), so the MLP's round-trip latency is
 // hidden behind the group's own gather instead of idling 4 of the SM's 32 warps.
+// level boundaries of the gather slices hidden in the five MMA waits of a tile: 0-4 | 4-SL1 | SL1-SL2 | SL2-SL3 | SL3-16
+#ifndef SL1
+#define SL1 7
+#define SL2 10
+#define SL3 13
+#endif
 template <int L0, int L1, bool IDX>
 __device__ __forceinline__ void gather_slice(const NetParams& P, const float4& s, uint32_t* f, uint32_t* idx_out) {
+  // two levels' loads in flight before either blend: measured 0.7 % faster than level by level (ptxas already
+  // overlaps most of it; 7 groups x 72 registers then spill 4 bytes)
 #pragma unroll
-  for (int l = L0; l < L1; ++l) {
-    LevelTaps A;
+  for (int l = L0; l < L1; l += 2) {
+    LevelTaps A, B;
     level_load<IDX>(P.lv[l], s.x, s.y, s.z, A, IDX && idx_out ? idx_out + l * 8 : nullptr);
+    if (l + 1 < L1) level_load<IDX>(P.lv[l + 1], s.x, s.y, s.z, B, IDX && idx_out ? idx_out + (l + 1) * 8 : nullptr);
     f[l] = level_blend(A);
+    if (l + 1 < L1) f[l + 1] = level_blend(B);
   }
 }
 
@@ -407,7 +417,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     tmem_wait_st();
     GROUP_SYNC();
     ISSUE(16, 64, 16, W1_OFF, 0);
-    if (has_next) gather_slice<4, 7, false>(P, sn, fn, nullptr);
+    if (has_next) gather_slice<4, SL1, false>(P, sn, fn, nullptr);
     // SH coefficients of the direction (per ray)
     uint32_t sh[8];
     if (dirs_mode == 0) {
@@ -442,7 +452,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     tmem_wait_st();
     GROUP_SYNC();
     ISSUE(32, 32, 64, V0_OFF, 0);
-    if (has_next) gather_slice<7, 10, false>(P, sn, fn, nullptr);
+    if (has_next) gather_slice<SL1, SL2, false>(P, sn, fn, nullptr);
     MMA_WAIT();
     ld_relu_pack32(t_d + lane_off, h);
     GROUP_SYNC();
@@ -455,7 +465,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     tmem_wait_st();
     GROUP_SYNC();
     ISSUE(32, 64, 64, V1_OFF, 0);
-    if (has_next) gather_slice<10, 13, false>(P, sn, fn, nullptr);
+    if (has_next) gather_slice<SL2, SL3, false>(P, sn, fn, nullptr);
     MMA_WAIT();
     ld_relu_pack32(t_d + lane_off, h);
     GROUP_SYNC();
@@ -468,7 +478,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     tmem_wait_st();
     GROUP_SYNC();
     ISSUE(16, 64, 16, V2_OFF, 0);
-    if (has_next) gather_slice<13, 16, false>(P, sn, fn, nullptr);
+    if (has_next) gather_slice<SL3, 16, false>(P, sn, fn, nullptr);
     MMA_WAIT();
     {
       uint32_t a[16];
