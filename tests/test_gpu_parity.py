@@ -521,3 +521,55 @@ def test_async_frames_growth_covers_every_enqueued_frame(pair):
     assert np.array_equal(r2.render_frame(intr, pose)[0], big)
     r2.close()
     r3.close()
+
+
+def test_full_size_c3_frame(built_lib):
+    """BASELINE.json's headline configuration at full size: C3, 1920x1080, bound 16, 5 cascades, T = 2^19 (the frame
+    bench.py times).  The oracle cannot render 2 M rays in seconds, so the frame is checked (a) against the oracle on
+    three bands of full pixel rows (top, through the centre, bottom: 11 520 rays, every cascade crossed), counts
+    bit-exact and colour / depth within the image tolerance; (b) through size-independent properties: rendering the
+    same pose again, and after another pose, gives identical bytes; a 3-way tile-sharded render assembles to the same
+    bytes and the shards' sample totals add up to the whole frame's; every ray's composited count is within
+    [0, 1024] and the emitted total is at least the composited total."""
+    import torch
+    from nerf_cuda_b200.multigpu import FrameSharding
+    import bench
+    cfg, W, H, _ = bench.WORKLOADS["C3"]
+    sc = syn.make_scene(cfg)
+    poses = bench.poses_for("C3")
+    intr = syn.intrinsics(W, H)
+    r = NerfRender(1)
+    r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    r.set_resolution((W, H))
+    u8 = r.render_frame(intr, poses[1])[0].copy()
+    rgb, dep, cnt = (x.copy() for x in r.float_frame())
+    n_whole = r.stats().n_samples
+    assert u8.shape == (H, W, 3) and cnt.min() >= 0 and cnt.max() <= 1024 and n_whole >= int(cnt.sum()) > 0
+    O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
+    for row in (3, H // 2 - 1, H - 5):
+        pix0, npix = row * W, 2 * W
+        rgb2, dep2, cnt2 = O.render(intr, poses[1], W, H, pix0, npix)
+        sl = slice(pix0, pix0 + npix)
+        assert np.array_equal(cnt[sl], cnt2), row
+        assert np.abs(rgb[sl] - rgb2).max() <= IMG_TOL and np.abs(dep[sl] - dep2).max() <= 1e-3, row
+    # idempotence, also across another pose (buffers regrown, t-cache and records rewritten in between)
+    assert np.array_equal(r.render_frame(intr, poses[1])[0], u8)
+    r.render_frame(intr, poses[2])
+    assert np.array_equal(r.render_frame(intr, poses[1])[0], u8)
+    r.close()
+    # tile sharding at full size
+    world = 3
+    sh = FrameSharding(W, H, world)
+    g = torch.zeros(world, sh.tiles_per_shard, 32, 32, 3, dtype=torch.uint8)
+    total = 0
+    for s in range(world):
+        rs = NerfRender(1)
+        rs.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+        rs.set_shard(s, world)
+        rs.set_resolution((W, H))
+        tiles = rs.render_frame(intr, poses[1])[0]
+        g[s, : tiles.shape[0]] = torch.from_numpy(tiles.copy())
+        total += rs.stats().n_samples
+        rs.close()
+    assert total == n_whole
+    assert np.array_equal(sh.assemble(g).numpy(), u8)
