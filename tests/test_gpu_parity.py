@@ -523,7 +523,8 @@ def test_async_frames_growth_covers_every_enqueued_frame(pair):
     r3.close()
 
 
-def test_full_size_c3_frame(built_lib):
+@pytest.mark.parametrize("pi", [1, 2])   # a typical pose (45 M samples) and one along the ground slab (180 M)
+def test_full_size_c3_frame(built_lib, pi):
     """BASELINE.json's headline configuration at full size: C3, 1920x1080, bound 16, 5 cascades, T = 2^19 (the frame
     bench.py times).  The oracle cannot render 2 M rays in seconds, so the frame is checked (a) against the oracle on
     three bands of full pixel rows (top, through the centre, bottom: 11 520 rays, every cascade crossed), counts
@@ -541,21 +542,21 @@ def test_full_size_c3_frame(built_lib):
     r = NerfRender(1)
     r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
     r.set_resolution((W, H))
-    u8 = r.render_frame(intr, poses[1])[0].copy()
+    u8 = r.render_frame(intr, poses[pi])[0].copy()
     rgb, dep, cnt = (x.copy() for x in r.float_frame())
     n_whole = r.stats().n_samples
     assert u8.shape == (H, W, 3) and cnt.min() >= 0 and cnt.max() <= 1024 and n_whole >= int(cnt.sum()) > 0
     O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
     for row in (3, H // 2 - 1, H - 5):
         pix0, npix = row * W, 2 * W
-        rgb2, dep2, cnt2 = O.render(intr, poses[1], W, H, pix0, npix)
+        rgb2, dep2, cnt2 = O.render(intr, poses[pi], W, H, pix0, npix)
         sl = slice(pix0, pix0 + npix)
         assert np.array_equal(cnt[sl], cnt2), row
         assert np.abs(rgb[sl] - rgb2).max() <= IMG_TOL and np.abs(dep[sl] - dep2).max() <= 1e-3, row
     # idempotence, also across another pose (buffers regrown, t-cache and records rewritten in between)
-    assert np.array_equal(r.render_frame(intr, poses[1])[0], u8)
-    r.render_frame(intr, poses[2])
-    assert np.array_equal(r.render_frame(intr, poses[1])[0], u8)
+    assert np.array_equal(r.render_frame(intr, poses[pi])[0], u8)
+    r.render_frame(intr, poses[3 - pi])
+    assert np.array_equal(r.render_frame(intr, poses[pi])[0], u8)
     r.close()
     # tile sharding at full size
     world = 3
@@ -567,7 +568,7 @@ def test_full_size_c3_frame(built_lib):
         rs.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
         rs.set_shard(s, world)
         rs.set_resolution((W, H))
-        tiles = rs.render_frame(intr, poses[1])[0]
+        tiles = rs.render_frame(intr, poses[pi])[0]
         g[s, : tiles.shape[0]] = torch.from_numpy(tiles.copy())
         total += rs.stats().n_samples
         rs.close()
