@@ -556,7 +556,8 @@ template <int MODE, int G>
 static void net_attr() {
   // 20.6 KB of shared memory per SM; leave the rest of the unified array to L1 (carveout in percent of 228 KB)
   cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NET_SMEM);
-  cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributePreferredSharedMemoryCarveout, 16);
+  static const int carveout = getenv("NRF_NET_CARVEOUT") ? atoi(getenv("NRF_NET_CARVEOUT")) : 16;
+  cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
 }
 static int g_net_groups = 7;   // measured on B200 (C3): 7 groups = 896 threads x 72 registers, no spills: 3-4 % faster than 8 x 64 (spills), 6 is slower again
 static void nrf_network_setup() {
