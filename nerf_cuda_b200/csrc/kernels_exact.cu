@@ -16,6 +16,7 @@
 
 #define RAYS_BLOCK 128
 #define RAYS_MIN_BLOCKS 8
+#define EMIT_CHUNK 8
 #ifndef COUNT_MIN_BLOCKS
 #define COUNT_MIN_BLOCKS 8   // k_rays_count: 47 registers = 10 resident blocks; asking for 10 or 12 measured 3 % / 14 % slower
 #endif
@@ -421,26 +422,34 @@ k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ 
     // cached t (the clamp to the box is the identity inside it, so both march variants give these same values)
     const float* tc = tcache + (size_t)(q >> 5) * (32 * NRF_TCACHE) + lane;
     const int nrep = min(c_total, NRF_TCACHE);
-    float t0 = __ldg(tc);
-    for (; c < nrep; ++c) {
-      const float tn = (c + 1 < nrep) ? __ldg(tc + 32 * (c + 1)) : 0.f;
-      const float x = clampf(R.o[0] + t0 * R.d[0], -R.bound, R.bound);
-      const float y = clampf(R.o[1] + t0 * R.d[1], -R.bound, R.bound);
-      const float z = clampf(R.o[2] + t0 * R.d[2], -R.bound, R.bound);
-      const float dt = clampf(t0 * R.dt_gamma, R.dt_min, R.dt_max);
-      t = t0 + dt;
-      const long long k = off + __popc(alive & lt);
-      if (t_rec) {   // frame path (SampleSrc): ray index in the fourth component, the sample's t beside it
-        samples[k] = make_float4(P.pos_w * x + 0.5f, P.pos_w * y + 0.5f, P.pos_w * z + 0.5f, __int_as_float(q));
-        t_rec[k] = t0;
-      } else {
-        samples[k] = make_float4(P.pos_w * x + 0.5f, P.pos_w * y + 0.5f, P.pos_w * z + 0.5f, dt);
-        t_after[k] = t;
-        sample_ray[k] = q;
+    // chunks of EMIT_CHUNK samples: all their cached t in flight at once (one L2 / HBM latency per chunk, not per sample)
+    while (c < nrep) {
+      float tq[EMIT_CHUNK];
+#pragma unroll
+      for (int j = 0; j < EMIT_CHUNK; ++j) tq[j] = (c + j < nrep) ? __ldg(tc + 32 * (c + j)) : 0.f;
+#pragma unroll
+      for (int j = 0; j < EMIT_CHUNK; ++j) {
+        if (c < nrep) {
+          const float t0 = tq[j];
+          const float x = clampf(R.o[0] + t0 * R.d[0], -R.bound, R.bound);
+          const float y = clampf(R.o[1] + t0 * R.d[1], -R.bound, R.bound);
+          const float z = clampf(R.o[2] + t0 * R.d[2], -R.bound, R.bound);
+          const float dt = clampf(t0 * R.dt_gamma, R.dt_min, R.dt_max);
+          t = t0 + dt;
+          const long long k = off + __popc(alive & lt);
+          if (t_rec) {   // frame path (SampleSrc): ray index in the fourth component, the sample's t beside it
+            samples[k] = make_float4(P.pos_w * x + 0.5f, P.pos_w * y + 0.5f, P.pos_w * z + 0.5f, __int_as_float(q));
+            t_rec[k] = t0;
+          } else {
+            samples[k] = make_float4(P.pos_w * x + 0.5f, P.pos_w * y + 0.5f, P.pos_w * z + 0.5f, dt);
+            t_after[k] = t;
+            sample_ray[k] = q;
+          }
+          off += __popc(alive);
+          alive &= ~died[warp][c];
+          ++c;
+        }
       }
-      off += __popc(alive);
-      alive &= ~died[warp][c];
-      t0 = tn;
     }
   }
   while (t < far && c < c_total) {
