@@ -629,6 +629,10 @@ static inline uint8_t* peer_slot_ptr(nrf_ctx* c) { return c->peer_frame + (size_
 // memory, k_emit / k_network / k_composite read it there; the sample buffers keep the capacity of earlier frames.
 // If the total exceeds the capacity the overflowing patches are skipped on the device (k_emit marks them) and
 // frame_check() — at the next host sync — grows the buffers and asks for the frame to be rendered again.
+// samples one frame can hold: the three per-sample buffers normally grow together, but the density-grid pass sizes
+// two of them on its own
+static size_t frame_capacity(const Device& D) { return std::min(D.samples.n, std::min(D.t0rec.n, D.sample_out.n)); }
+
 static SampleSrc sample_src(const Device& D) {
   SampleSrc s{};
   s.t0 = D.t0rec.p;
@@ -644,7 +648,7 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
     const size_t want = std::max<size_t>((size_t)D.n_local * 32, 4096);
     CU(D.samples.ensure(want)); CU(D.t0rec.ensure(want)); CU(D.sample_out.ensure(want));
   }
-  const size_t cap = std::min<size_t>(std::min(D.samples.n, std::min(D.t0rec.n, D.sample_out.n)), (1ull << 31) - 256);
+  const size_t cap = std::min<size_t>(frame_capacity(D), (1ull << 31) - 256);
   const SampleSrc src = sample_src(D);
   CU(cudaEventRecord(D.ev[0], D.stream));
   if (D.n_local > 0) {
@@ -695,7 +699,7 @@ static int frame_check(nrf_ctx*, Device& D, bool& redo) {
   CU(cudaMemsetAsync(D.total.p + 1, 0, sizeof(unsigned long long), D.stream));   // restart the running maximum
   if (mx > (1ull << 31) - 256) return fail(NRF_EINVAL, "frame produces %llu samples (> 2^31)", mx);
   D.last_samples = S;
-  const size_t cap = std::min(D.samples.n, std::min(D.t0rec.n, D.sample_out.n));
+  const size_t cap = frame_capacity(D);
   if (mx > cap) {
     const size_t want = (size_t)mx + (size_t)mx / 4;
     CU(D.samples.ensure(want)); CU(D.t0rec.ensure(want)); CU(D.sample_out.ensure(want));
@@ -809,7 +813,7 @@ extern "C" int nrf_render_batch(nrf_ctx* c, const float intr[4], const float* po
     const int slot = j & 1;
     CU(cudaEventSynchronize(c->batch_ev[slot]));
     bool over = false;
-    for (size_t g = 0; g < c->devs.size(); ++g) over |= c->devs[g].total_h[4 * (fno[slot][g] & 3u)] > c->devs[g].samples.n;
+    for (size_t g = 0; g < c->devs.size(); ++g) over |= c->devs[g].total_h[4 * (fno[slot][g] & 3u)] > frame_capacity(c->devs[g]);
     if (over) redo.push_back(j);
     else std::memcpy(rgb_out + (size_t)j * frame_bytes, c->batch_stage[slot], frame_bytes);
     return NRF_OK;
