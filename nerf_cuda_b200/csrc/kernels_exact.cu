@@ -9,9 +9,10 @@
 //   init_step0 (:221-239), kernel_compact_rays (:394-415), kernel_march_rays (:524-655),
 //   linear_transformer x2 (include/nerf-cuda/common_device.cuh:31-36), concat_network_in_and_out (:280-306).
 // Design: one pass over whole rays instead of a host-driven <=8-step wavefront with a blocking D2H per iteration
-// (src/nerf_render.cu:269-338).  Pass 1 counts samples per ray and reduces per block; a one-block scan gives block
-// bases; pass 2 re-marches (from the first sample on) and writes a COMPACT sample list, step-interleaved inside each
-// warp of 32 neighbouring rays (ballot/popc position arithmetic, see k_emit).
+// (src/nerf_render.cu:269-338).  Pass 1 counts samples per ray, caches the t of each ray's first NRF_TCACHE samples and
+// reduces per block; a one-block scan gives block bases; pass 2 replays the cached samples (marching again only beyond
+// them) and writes a COMPACT sample list, step-interleaved inside each warp of 32 neighbouring rays (ballot/popc
+// position arithmetic, see k_emit).
 #include "nrf_device.cuh"
 
 #define RAYS_BLOCK 128
@@ -364,14 +365,16 @@ extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict
   }
 }
 
-// Pass 2: re-march (from t_first) and emit the compact sample list in WARP-INTERLEAVED order: the samples of one warp
+// Pass 2: replay the t-cache (re-march only beyond it; the probe path re-marches from t_first) and emit the compact
+// sample list in WARP-INTERLEAVED order: the samples of one warp
 // (32 neighbouring rays, an 8x4 pixel patch) are stored step-major — step k of every ray that has a k-th sample, in
 // lane order, then step k+1 ... — so 32 consecutive samples are spatial neighbours (one thin slab of the patch), which
 // is what makes the hash-grid gather cache-coherent.  Position of (lane r, step k):
 //     warp_base + sum_{r'} min(c_r', k) + #{r' < r : c_r' > k}
 // evaluated incrementally per lane from a per-warp table died[k] = {r' : c_r' == k+1} in shared memory, so lanes do not
 // march in lockstep.  warp_base[] (first sample of every warp) is kept for the composite kernel.
-// samples: float4 {u,v,w,dt} (position already normalised: x*pos_w+0.5, nerf_render.cu:311-312), t_after, ray id.
+// Frame path (t_rec != null): samples float4 {u,v,w, ray id} + t_rec = the sample's t (SampleSrc, nrf_device.cuh).
+// Probe path: samples float4 {u,v,w,dt} (position already normalised: x*pos_w+0.5, nerf_render.cu:311-312), t_after, ray id.
 // dbg (optional, probe only): per sample {x,y,z,dt,t_after,level,cell,ray} raw, RAY-major at dbg_offsets[q] + k.
 extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, RAYS_MIN_BLOCKS)
 k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays, const float2* __restrict__ far_tf,
