@@ -18,6 +18,7 @@
 #include <utility>
 
 #include "../nerf_b200.h"
+#include "../nerf_b200_ext.h"
 
 namespace ngp {
 
@@ -81,6 +82,14 @@ class NerfRender {
     for (int r = 0; r < 4; ++r)
       for (int c = 0; c < 4; ++c) p[r * 4 + c] = pos(r, c);
     return render_frame(cam, p);
+  }
+
+  // Extension (no reference counterpart): n poses in one call through the two-deep pipeline of nrf_render_batch (frame
+  // i+1 renders while frame i is copied out).  rgb_out: caller-owned n*W*H*3 bytes; depth_out: n*W*H bytes or null.
+  void render_batch(Camera cam, const float* poses_rowmajor, int n_poses, unsigned char* rgb_out,
+                    unsigned char* depth_out = nullptr) {
+    const float intr[4] = {cam.fl_x, cam.fl_y, cam.cx, cam.cy};
+    check(nrf_render_batch_rgbd(ctx_, intr, poses_rowmajor, n_poses, rgb_out, depth_out));
   }
 
   // nerf_render.cu:369-386: in the reference this fills rays_o/rays_d of one GPU; ray generation is fused into the

@@ -67,7 +67,7 @@ typedef struct nrf_model_desc {
 /* Per-frame statistics (SURVEY.md §5 metrics row). Times are CUDA-event milliseconds on GPU 0's stream. */
 typedef struct nrf_stats {
   uint64_t n_rays;        /* rays of the last frame (W*H)                                   */
-  uint64_t n_samples;     /* samples emitted by the march (all GPUs)                        */
+  uint64_t n_samples;     /* samples evaluated by the network (all GPUs)                    */
   uint64_t n_hit_rays;    /* rays with at least one sample                                  */
   float ms_total;         /* whole frame, device time                                       */
   float ms_setup;         /* ray generation + aabb                                          */
@@ -76,6 +76,10 @@ typedef struct nrf_stats {
   float ms_composite;     /* composite + finalise                                           */
   uint32_t n_launches;    /* kernels launched for the last frame                            */
   uint32_t n_gpus;
+  uint64_t n_samples_marched; /* samples the occupancy march found on all rays (schedule-independent)          */
+  uint64_t n_samples_used;    /* samples composited before the rays terminated (T < 1e-4, render_utils.h:727)  */
+  uint32_t n_rounds;          /* evaluation rounds of the frame: 1 = whole rays, > 1 = termination-aware        */
+  uint32_t reserved;
 } nrf_stats;
 
 typedef struct nrf_ctx nrf_ctx;

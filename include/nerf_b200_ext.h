@@ -55,8 +55,25 @@ int nrf_peer_frame_to_host(nrf_ctx* ctx, uint8_t** rgb, uint8_t** depth);
  * reference has no equivalent: it blocks on a device->host read after every <= 8 march steps (nerf_render.cu:291). */
 int nrf_overflowed_frames(nrf_ctx* ctx, uint64_t* n_frames);
 
+/* nrf_render_batch with the depth channel: depth_out (may be NULL) receives n * W*H bytes, frame after frame, the u8
+ * depth of struct Image (common.h:76-89) that the reference computes but never sends (render_server.cu:101). */
+int nrf_render_batch_rgbd(nrf_ctx* ctx, const float intr[4], const float* poses_rowmajor, int n_poses, uint8_t* rgb_out,
+                          uint8_t* depth_out);
+
+/* Termination-aware evaluation.  The reference kills a ray as soon as its transmittance falls below 1e-4
+ * (render_utils.h:727, rays_t = -1) and compacts it away before its next wavefront of <= 8 steps (kernel_compact_rays,
+ * render_utils.h:394-415; nerf_render.cu:278-302), so samples behind an opaque surface never reach its network.  Here a
+ * frame is evaluated in ROUNDS of samples per ray — by default [0,16), [16,64), [64,1024) — each round marching,
+ * evaluating and compositing only the rays still alive, all enqueued without a host round trip.  mode 0: one round (whole
+ * rays; right when almost nothing terminates, e.g. random-init weights); 1: rounds always; 2 (default): automatic — rounds
+ * are switched on when the last validated frame composited < 3/4 of the samples its march found and off again above
+ * 9/10.  The pixels, depths and composited counts are identical in every mode.  bounds/n_bounds (NULL/0 = keep): the
+ * cumulative per-ray sample boundaries of all rounds but the last (1..3 values, ascending, < NRF_MAX_STEPS). */
+int nrf_set_termination(nrf_ctx* ctx, int mode, const int* bounds, int n_bounds);
+
 /* Memory micro-benchmarks on device 0 (roofline denominators for the hash gather).  mode 0: coalesced
- * 16-byte streaming reads over a window (window <= L2 size => L2->SM bandwidth, window >> L2 => HBM read bandwidth);
+ * 16-byte streaming reads over a window split across the CTAs (window >> L2 => HBM read bandwidth); mode 2: every CTA
+ * streams the WHOLE window (per-SM footprint = window, so the SM's own L1 cannot serve it: window <= L2 => L2->SM bandwidth);
  * mode 1: one random 8-byte slot per lane (one 32-byte sector in its own 128-byte line: the access shape of a hashed
  * grid level).  *gbs = requested bytes per second / 1e9; *gloads (may be NULL) = loads per nanosecond. */
 int nrf_bench_memory(nrf_ctx* ctx, int mode, size_t window_bytes, int iters, float* gbs, float* gloads);

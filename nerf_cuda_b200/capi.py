@@ -28,7 +28,8 @@ class Stats(C.Structure):
     _fields_ = [("n_rays", C.c_uint64), ("n_samples", C.c_uint64), ("n_hit_rays", C.c_uint64),
                 ("ms_total", C.c_float), ("ms_setup", C.c_float), ("ms_march", C.c_float),
                 ("ms_network", C.c_float), ("ms_composite", C.c_float), ("n_launches", C.c_uint32),
-                ("n_gpus", C.c_uint32)]
+                ("n_gpus", C.c_uint32), ("n_samples_marched", C.c_uint64), ("n_samples_used", C.c_uint64),
+                ("n_rounds", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 EXPORTS = [
@@ -133,14 +134,18 @@ class NerfRender:
         intr, pose = _f32(cam).reshape(4), _f32(pos).reshape(16)
         _check(self._l.nrf_render_frame_device(self._ctx, _p(intr, C.c_float), _p(pose, C.c_float)))
 
-    def render_batch(self, cam, poses):
+    def render_batch(self, cam, poses, want_depth=False):
         intr, poses = _f32(cam).reshape(4), _f32(poses).reshape(-1, 16)
         whole = self._shard[1] == 1
         n = self.W * self.H if whole else self.local_rays()
         out = np.zeros((poses.shape[0], n, 3), np.uint8)
-        _check(self._l.nrf_render_batch(self._ctx, _p(intr, C.c_float), _p(poses, C.c_float), poses.shape[0],
-                                        _p(out, C.c_uint8)))
-        return out.reshape(poses.shape[0], self.H, self.W, 3) if whole else out.reshape(poses.shape[0], -1, 32, 32, 3)
+        dep = np.zeros((poses.shape[0], n), np.uint8) if want_depth else None
+        _check(self._l.nrf_render_batch_rgbd(self._ctx, _p(intr, C.c_float), _p(poses, C.c_float), poses.shape[0],
+                                             _p(out, C.c_uint8), _p(dep, C.c_uint8)))
+        out = out.reshape(poses.shape[0], self.H, self.W, 3) if whole else out.reshape(poses.shape[0], -1, 32, 32, 3)
+        if not want_depth:
+            return out
+        return out, (dep.reshape(poses.shape[0], self.H, self.W) if whole else dep.reshape(poses.shape[0], -1, 32, 32))
 
     def float_frame(self):
         """Float image of the last frame + composited samples per ray: global pixel order [W*H] for a whole-frame
@@ -238,6 +243,12 @@ class NerfRender:
                                        color_space, C.c_float(exposure), _p(bg, C.c_float), output_color_space,
                                        tonemap_curve, int(bool(clamp)), _p(out, C.c_float)))
         return accum, out
+
+    def set_termination(self, mode=2, bounds=None):
+        """Termination-aware evaluation rounds (nerf_b200_ext.h nrf_set_termination): mode 0 whole rays, 1 rounds,
+        2 automatic; bounds = cumulative per-ray sample boundaries of all rounds but the last (default 16, 64)."""
+        b = (C.c_int * len(bounds))(*bounds) if bounds else None
+        _check(self._l.nrf_set_termination(self._ctx, int(mode), b, len(bounds) if bounds else 0))
 
     def overflowed_frames(self) -> int:
         """Asynchronous frames that did not fit the sample buffers so far (nerf_b200_ext.h nrf_overflowed_frames)."""

@@ -13,17 +13,27 @@
 
 #define COMP_CHUNK 8
 
+// Evaluation rounds (termination-aware frames, RoundWin R): this launch composites the samples with step index in
+// [RW.s0, RW.s1) — the list k_emit wrote for the same window — and carries each ray's accumulators between rounds in
+// RW.st (two float4 per ray: {wsum, depth, t, last_t}, {r, g, b, samples used}).  A ray whose transmittance fell below
+// 1e-4 is marked in RW.dead: the next round neither marches, evaluates nor composites it — the reference drops such a
+// ray from its next wavefront the same way (render_utils.h:727 rays_t = -1, kernel_compact_rays :394-415).  The
+// operations on a ray and their order do not depend on the round schedule, so every schedule gives identical pixels.
+// RW.first: start from fresh accumulators; RW.last: finalise and write the pixels.  A whole-ray frame is one round with both.
 extern "C" __global__ void __launch_bounds__(128)
 k_composite(int n_rays, ShardMap map, const int* __restrict__ warp_base, const int* __restrict__ counts,
             const float4* __restrict__ rays, const float2* __restrict__ far_tf, const __grid_constant__ SampleSrc S,
             const uint2* __restrict__ sample_out, float* __restrict__ rgb_f32,
             float* __restrict__ depth_f32, int* __restrict__ used_counts, uint8_t* __restrict__ rgb_u8,
-            uint8_t* __restrict__ depth_u8, int u8_pixel_order) {
+            uint8_t* __restrict__ depth_u8, int u8_pixel_order, const __grid_constant__ RoundWin RW,
+            unsigned long long* __restrict__ used_total) {
   const int lane = threadIdx.x & 31;
   const int q = blockIdx.x * blockDim.x + threadIdx.x;   // n_rays is a multiple of 32: whole warps only
   if (q >= n_rays) return;
   const int wb = warp_base[q >> 5];
-  const int cnt = wb < 0 ? 0 : counts[q];   // wb < 0: the patch did not fit the sample buffers (frame will be redone)
+  const bool was_dead = !RW.first && RW.dead[q];
+  // wb < 0: the patch did not fit the sample buffers (frame will be redone)
+  const int cnt = (wb < 0 || was_dead) ? 0 : max(0, min(counts[q], RW.s1) - RW.s0);
   const float4 ray = rays[q];
   const float near = ray.w, far = far_tf[q].x;
   int cmax = cnt;
@@ -34,7 +44,13 @@ k_composite(int n_rays, ShardMap map, const int* __restrict__ warp_base, const i
   float wsum = 0.f, dep = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
   float tc = near, last_t = near;
   int used = 0;
-  bool running = true;
+  bool running = !was_dead;
+  if (!RW.first) {
+    const float4 a = RW.st[2 * (size_t)q], b = RW.st[2 * (size_t)q + 1];
+    wsum = a.x; dep = a.y; tc = a.z; last_t = a.w;
+    cr = b.x; cg = b.y; cb = b.z; used = __float_as_int(b.w);
+  }
+  const int used0 = used;
   // The steps of a ray are sequential, but WHERE its samples live is not data-dependent (ballot/popc of the counts), so
   // the loop runs in chunks of COMP_CHUNK steps: all indices first, then all loads in flight at once, then the
   // sequential accumulation.  Without this the kernel's critical path is one DRAM latency per step of its longest ray
@@ -83,6 +99,16 @@ k_composite(int n_rays, ShardMap map, const int* __restrict__ warp_base, const i
       }
     }
     if (!__any_sync(0xffffffffu, running && k0 + COMP_CHUNK < cnt)) break;
+  }
+  if (used_total) {   // samples composited by this launch (one atomic per warp that used any)
+    const int wu = __reduce_add_sync(0xffffffffu, used - used0);
+    if (lane == 0 && wu) atomicAdd(used_total, (unsigned long long)wu);
+  }
+  if (!RW.last) {
+    RW.st[2 * (size_t)q] = make_float4(wsum, dep, tc, last_t);
+    RW.st[2 * (size_t)q + 1] = make_float4(cr, cg, cb, __int_as_float(used));
+    RW.dead[q] = running ? 0 : 1;
+    return;
   }
   const float bg = 1.0f;  // m_bg_color, nerf_render.h:74
   const float R = cr + (1.0f - wsum) * bg, G = cg + (1.0f - wsum) * bg, B = cb + (1.0f - wsum) * bg;

@@ -266,10 +266,13 @@ __device__ __forceinline__ void block_total(int c, int* __restrict__ block_sums)
 
 // Pass 1: rays of this shard (patch-major order, ShardMap) + sample counts + per-block totals.
 // rays: float4 {dx,dy,dz,near}; far_tf: float2 {far, t_first}; counts; block_sums[gridDim.x]
+// s1: samples per ray the FIRST evaluation round takes (NRF_MAX_STEPS_D = the whole ray; termination-aware frames take
+// fewer, see k_round_sums); block_sums then holds the round's totals.  frame_tot[0] += all samples found (one atomic
+// per block), so the host learns how many samples the march produced whatever the round schedule was.
 extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, COUNT_MIN_BLOCKS)
 k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, float4* __restrict__ rays,
              float2* __restrict__ far_tf, int* __restrict__ counts, int* __restrict__ block_sums,
-             uint4* __restrict__ ray_sh, float* __restrict__ tcache) {
+             uint4* __restrict__ ray_sh, float* __restrict__ tcache, int s1, unsigned long long* __restrict__ frame_tot) {
   __shared__ float lut[NRF_MAX_GRID + 1 + LUT_CONST];
   load_lut(P, lut);
   const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
@@ -293,6 +296,29 @@ k_rays_count(const __grid_constant__ MarchParams P, ShardMap map, int n_local, f
       ray_sh[2 * (size_t)q + 1] = make_uint4(sh[4], sh[5], sh[6], sh[7]);
     }
   }
+  block_total(min(c, s1), block_sums);
+  {
+    __shared__ int marched[RAYS_BLOCK / 32];
+    const int wsum_c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0) marched[threadIdx.x >> 5] = wsum_c;
+    __syncthreads();
+    if (threadIdx.x == 0 && frame_tot) {
+      int m = 0;
+#pragma unroll
+      for (int w = 0; w < RAYS_BLOCK / 32; ++w) m += marched[w];
+      if (m) atomicAdd(frame_tot, (unsigned long long)m);
+    }
+  }
+}
+
+// Later evaluation rounds of a termination-aware frame: per-block totals of the samples with step index in [s0, s1) of
+// the rays that are still alive (dead[q] set by k_composite when a ray's transmittance fell below 1e-4).
+extern "C" __global__ void __launch_bounds__(RAYS_BLOCK)
+k_round_sums(int n, const int* __restrict__ counts, const uint8_t* __restrict__ dead, int s0, int s1,
+             int* __restrict__ block_sums) {
+  const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
+  int c = 0;
+  if (q < n && !dead[q]) c = max(0, min(counts[q], s1) - s0);
   block_total(c, block_sums);
 }
 
@@ -328,20 +354,23 @@ k_count_given(const __grid_constant__ MarchParams P, int n, const float4* __rest
   block_total(c, block_sums);
 }
 
-// One-block exclusive scan of the per-block totals (in place); total[0] = sum.  n_blocks <= 1024*64.
-// total[0] = samples of this frame; total[1] = running maximum over the frames since the host last looked (buffer growth:
-// frames are enqueued without host syncs); total[2] = number of frames whose samples did not fit `capacity`.
+// One-block exclusive scan of the per-block totals (in place).  n_blocks <= 1024*64.  The running prefix is kept in 64
+// bits and the stored block bases saturate at INT_MAX, so a frame with more than 2^31 samples cannot wrap to a small
+// positive base: its patches fail k_emit's capacity test (capacity < 2^31) and the frame is reported as overflowed.
+// total[] (TOT_* in nrf_api.cu): [0] samples of this round; [1] running maximum of [0] since the host last looked
+// (buffer growth: frames are enqueued without host syncs); [2] rounds that did not fit `capacity`, cumulative;
+// [4] += samples of this round (evaluated samples of the frame); [6] = 1 if a round of this frame did not fit.
 extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict__ block_sums, int n_blocks,
                                                                  unsigned long long* __restrict__ total,
                                                                  unsigned long long capacity) {
   __shared__ int wsum[32];
-  __shared__ int carry_s;
+  __shared__ long long carry_s;
   if (threadIdx.x == 0) carry_s = 0;
   __syncthreads();
   for (int base = 0; base < n_blocks; base += 1024) {
     const int i = base + threadIdx.x;
     const int v = (i < n_blocks) ? block_sums[i] : 0;
-    const int incl = warp_incl_scan(v);
+    const int incl = warp_incl_scan(v);   // <= 1024 blocks x 131072 samples = 2^27: no overflow inside one chunk
     if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = incl;
     __syncthreads();
     if (threadIdx.x < 32) {
@@ -350,9 +379,8 @@ extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict
       wsum[threadIdx.x] = wi - w;  // exclusive warp bases
     }
     __syncthreads();
-    const int carry = carry_s;
-    const int excl = carry + wsum[threadIdx.x >> 5] + incl - v;
-    if (i < n_blocks) block_sums[i] = excl;
+    const long long excl = carry_s + wsum[threadIdx.x >> 5] + incl - v;
+    if (i < n_blocks) block_sums[i] = (int)min(excl, (long long)0x7fffffff);
     __syncthreads();
     if (threadIdx.x == 1023) carry_s = excl + v;
     __syncthreads();
@@ -361,7 +389,8 @@ extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict
     const unsigned long long s = (unsigned long long)carry_s;
     total[0] = s;
     if (s > total[1]) total[1] = s;
-    if (s > capacity) total[2] += 1ull;
+    total[4] += s;
+    if (s > capacity) { total[2] += 1ull; total[6] = 1ull; }
   }
 }
 
@@ -376,19 +405,24 @@ extern "C" __global__ void __launch_bounds__(1024) k_scan_blocks(int* __restrict
 // Frame path (t_rec != null): samples float4 {u,v,w, ray id} + t_rec = the sample's t (SampleSrc, nrf_device.cuh).
 // Probe path: samples float4 {u,v,w,dt} (position already normalised: x*pos_w+0.5, nerf_render.cu:311-312), t_after, ray id.
 // dbg (optional, probe only): per sample {x,y,z,dt,t_after,level,cell,ray} raw, RAY-major at dbg_offsets[q] + k.
+// Evaluation rounds (termination-aware frames): only the samples with step index in [s0, s1) of rays that are still
+// alive are emitted (dead may be null = all alive); the list, warp_base and the block bases are those of THIS round.
+// A ray with samples beyond s1 leaves its march state (t after its last emitted sample) in t_resume for the next round.
 extern "C" __global__ void __launch_bounds__(RAYS_BLOCK, RAYS_MIN_BLOCKS)
 k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ rays, const float2* __restrict__ far_tf,
        const int* __restrict__ counts, const int* __restrict__ block_bases, int* __restrict__ warp_base,
        float4* __restrict__ samples, float* __restrict__ t_after, int* __restrict__ sample_ray,
        float* __restrict__ dbg, const long long* __restrict__ dbg_offsets, long long capacity,
-       const float* __restrict__ tcache, float* __restrict__ t_rec) {
+       const float* __restrict__ tcache, float* __restrict__ t_rec, int s0, int s1,
+       const uint8_t* __restrict__ dead, float* __restrict__ t_resume) {
   __shared__ float lut[NRF_MAX_GRID + 1 + LUT_CONST];
   __shared__ int wsum[RAYS_BLOCK / 32];
   __shared__ uint32_t died[RAYS_BLOCK / 32][NRF_MAX_STEPS_D];
   load_lut(P, lut);
   const int q = blockIdx.x * RAYS_BLOCK + threadIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int c_total = (q < n) ? counts[q] : 0;
+  const int c_all = (q < n) ? counts[q] : 0;
+  const int c_total = (q < n && !(dead && dead[q])) ? max(0, min(c_all, s1) - s0) : 0;   // this round's samples of the ray
   const int incl = warp_incl_scan(c_total);
   if (lane == 31) wsum[warp] = incl;
   // per-warp table of the lanes that run out of samples after step k
@@ -414,17 +448,17 @@ k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ 
   ray_ctx(P, lut, d, R);
   const float2 ft = far_tf[q];
   const float far = ft.x;
-  float t = ft.y;
+  float t = s0 == 0 ? ft.y : t_resume[q];
   int c = 0;
   long long off = base;
   const long long dbg0 = dbg ? dbg_offsets[q] : 0;
   Step s;
   const bool fast = P.fast;
-  if (tcache) {
+  if (tcache && s0 < NRF_TCACHE) {
     // replay the cached samples: position, dt and t_after are the occupied branch of march_step evaluated at the
     // cached t (the clamp to the box is the identity inside it, so both march variants give these same values)
-    const float* tc = tcache + (size_t)(q >> 5) * (32 * NRF_TCACHE) + lane;
-    const int nrep = min(c_total, NRF_TCACHE);
+    const float* tc = tcache + (size_t)(q >> 5) * (32 * NRF_TCACHE) + lane + 32 * s0;
+    const int nrep = min(c_total, NRF_TCACHE - s0);
     // chunks of EMIT_CHUNK samples: all their cached t in flight at once (one L2 / HBM latency per chunk, not per sample)
     while (c < nrep) {
       float tq[EMIT_CHUNK];
@@ -478,6 +512,7 @@ k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ 
     alive &= ~died[warp][c];
     ++c;
   }
+  if (t_resume && c_all > s1) t_resume[q] = t;   // march state for the next round: t after sample s1-1
 }
 
 // Load-time: float density grid -> occupancy bitfield, bit == (density > thresh)   (render_utils.h:560,619)

@@ -3,6 +3,10 @@
 //
 //   mode 0  streaming read   : every thread reads coalesced 16-byte words (L1 bypassed) over a window; a window that fits the 126 MB
 //                              L2 measures L2->SM bandwidth, a window far larger than L2 measures HBM read bandwidth.
+//   mode 2  streaming read, every CTA over the WHOLE window (rotated start): the per-SM footprint is the window itself, so
+//                              a 24 MB window cannot be served by the SM's own L1 (mode 0 splits the window over the
+//                              CTAs — 24 MB / 148 = 162 KB per SM, which fits L1, and ld.cg did not keep it out: the
+//                              round-1 log shows 28 TB/s for 24 MB against 12.9 TB/s for 64 MB).  This is the L2->SM figure.
 //   mode 1  sector gather    : every lane reads ONE 8-byte slot at a pseudo-random position of the window, i.e. one
 //                              32-byte sector in its own 128-byte line per lane — the access shape of a hashed level of
 //                              the grid (kernels_network.cu level_load: one LDG.64 per (y,z) corner pair).  It is bound by
@@ -25,6 +29,22 @@ k_probe_stream(const uint4* __restrict__ buf, size_t n_vec, int passes, uint32_t
     }
   }
   if (acc == 0x9e3779b9u) sink[0] = acc;  // never true for the zero-filled buffer; keeps the loads alive
+}
+
+__global__ void __launch_bounds__(PROBE_THREADS, 1)
+k_probe_stream_whole(const uint4* __restrict__ buf, size_t n_vec, int passes, uint32_t* __restrict__ sink) {
+  uint32_t acc = 0;
+  const size_t start = (n_vec / gridDim.x) * blockIdx.x;   // rotated start: the CTAs do not hit the same L2 lines in lockstep
+  for (int p = 0; p < passes; ++p) {
+#pragma unroll 4
+    for (size_t k = threadIdx.x; k < n_vec; k += PROBE_THREADS) {
+      size_t i = start + k;
+      if (i >= n_vec) i -= n_vec;
+      const uint4 v = __ldcg(buf + i);
+      acc ^= v.x ^ v.y ^ v.z ^ v.w;
+    }
+  }
+  if (acc == 0x9e3779b9u) sink[0] = acc;
 }
 
 __device__ __forceinline__ uint32_t mix32(uint32_t x) {
@@ -51,7 +71,9 @@ k_probe_gather(const uint2* __restrict__ buf, uint32_t slot_mask, int loads_per_
 
 extern "C" cudaError_t nrf_launch_probe(int mode, int sms, cudaStream_t stream, const void* buf, size_t bytes, int work,
                                         uint32_t* sink) {
-  if (mode == 0) {
+  if (mode == 2) {
+    k_probe_stream_whole<<<sms, PROBE_THREADS, 0, stream>>>(reinterpret_cast<const uint4*>(buf), bytes / 16, work, sink);
+  } else if (mode == 0) {
     k_probe_stream<<<sms, PROBE_THREADS, 0, stream>>>(reinterpret_cast<const uint4*>(buf), bytes / 16, work, sink);
   } else {
     uint32_t slots = 1;

@@ -29,7 +29,8 @@
 // kernels (kernels_exact.cu, kernels_network.cu, kernels_composite.cu)
 extern "C" {
 __global__ void k_rays_count(const MarchParams P, ShardMap map, int n_local, float4* rays, float2* far_tf, int* counts,
-                             int* block_sums, uint4* ray_sh, float* tcache);
+                             int* block_sums, uint4* ray_sh, float* tcache, int s1, unsigned long long* frame_tot);
+__global__ void k_round_sums(int n, const int* counts, const uint8_t* dead, int s0, int s1, int* block_sums);
 __global__ void k_rays_given_pixels(const MarchParams P, int pix0, int n, float4* rays, float* fars);
 __global__ void k_count_given(const MarchParams P, int n, const float4* rays, float2* far_tf, int* counts,
                               int* block_sums);
@@ -37,7 +38,7 @@ __global__ void k_scan_blocks(int* block_sums, int n_blocks, unsigned long long*
 __global__ void k_emit(const MarchParams P, int n, const float4* rays, const float2* far_tf, const int* counts,
                        const int* block_bases, int* warp_base, float4* samples, float* t_after, int* sample_ray,
                        float* dbg, const long long* dbg_offsets, long long capacity, const float* tcache,
-                       float* t_rec);
+                       float* t_rec, int s0, int s1, const uint8_t* dead, float* t_resume);
 __global__ void k_build_occupancy(const float* grid, uint32_t n_cells, float thresh, uint32_t* bits);
 __global__ void k_cast_half(const float* in, __half* out, size_t n);
 __global__ void k_accumulate(int n, const float4* frame, float4* accum, float sample_count, int color_space);
@@ -49,7 +50,7 @@ __global__ void k_dg_update(uint32_t n, const uint2* sample_out, float decay, in
 __global__ void k_composite(int n_rays, ShardMap map, const int* warp_base, const int* counts, const float4* rays,
                             const float2* far_tf, const SampleSrc S, const uint2* sample_out,
                             float* rgb_f32, float* depth_f32, int* used_counts, uint8_t* rgb_u8, uint8_t* depth_u8,
-                            int u8_pixel_order);
+                            int u8_pixel_order, const RoundWin R, unsigned long long* used_total);
 size_t nrf_network_smem_bytes();
 cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t stream, const NetParams* P, int n,
                                const float4* samples, const int* sample_ray, const float4* rays, const uint4* ray_sh,
@@ -173,6 +174,10 @@ static void pack_weight(const float* W, int n_out, int n_in, uint16_t* dst) {
 }
 
 // ---------------------------------------------------------------------------------------------------- context
+#define NRF_MAX_ROUNDS 4
+// device counters of a frame (Device::total; written by k_scan_blocks / k_rays_count / k_composite)
+enum { TOT_ROUND = 0, TOT_MAX = 1, TOT_OVF_EVENTS = 2, TOT_MARCHED = 3, TOT_EVAL = 4, TOT_USED = 5, TOT_FRAME_OVF = 6, TOT_N = 8 };
+
 template <typename T>
 struct DevBuf {
   T* p = nullptr;
@@ -213,20 +218,35 @@ struct Device {
   DevBuf<int> counts, warp_base, block_sums, sample_ray, used;
   DevBuf<uint2> sample_out;
   DevBuf<uint8_t> rgb_u8, depth_u8;
-  DevBuf<unsigned long long> total;
-  unsigned long long* total_h = nullptr;  // pinned
+  DevBuf<unsigned long long> total;        // TOT_N counters (below)
+  unsigned long long* total_h = nullptr;  // pinned: ring of 4 frames x TOT_N
+  // termination-aware frames (round schedule): per-ray accumulators, terminated flags and march state between rounds
+  DevBuf<float4> ray_state;
+  DevBuf<uint8_t> dead;
+  DevBuf<float> t_resume;
+  cudaEvent_t rev[NRF_MAX_ROUNDS][4] = {};   // rounds >= 1: start, after emit, after network, after composite
+  int rounds_timed = 1;                     // rounds of the frame the events above belong to
+  unsigned long long last_marched = 0, last_used = 0;
   // probe scratch
   DevBuf<uint4> enc;
   DevBuf<uint32_t> idx;
   DevBuf<float> dbg;
   unsigned long long last_samples = 0;
-  unsigned frame_no = 0;          // frames enqueued; {total, running max, overflowed frames} of frame f land in
-                                  // total_h[4 * (f & 3)] (k_scan_blocks)
+  unsigned frame_no = 0;          // frames enqueued; the counters of frame f land in total_h[TOT_N * (f & 3)]
   unsigned long long overflowed = 0;  // frames that did not fit the sample buffers (as of the last sync point)
 };
 
 struct nrf_ctx {
   std::vector<Device> devs;
+  // Evaluation rounds of a frame (cumulative step boundaries; the last is always NRF_MAX_STEPS_D).  One round = whole
+  // rays, what the headline benchmark runs.  Termination-aware: {16, 64, 1024} — rays that turned opaque in a round are
+  // neither marched, evaluated nor composited in the next (the reference drops them from its next <= 8-step wavefront,
+  // render_utils.h:727 + :394-415).  term_mode 0 = off, 1 = on, 2 = auto: switched on when the last validated frame
+  // composited less than 3/4 of the samples its march produced, off again above 9/10.  Pixels do not depend on it.
+  int term_mode = 2;
+  bool chunked = false;
+  int round_bounds[NRF_MAX_ROUNDS] = {16, 64, NRF_MAX_STEPS_D, NRF_MAX_STEPS_D};
+  int n_round_bounds = 3;
   nrf_model_desc desc{};
   HostLevels levels{};
   float aabb[6] = {};
@@ -245,6 +265,9 @@ struct nrf_ctx {
   uint8_t* depth_host = nullptr;  // pinned, W*H
   uint8_t* batch_stage[2] = {nullptr, nullptr};   // pinned staging of nrf_render_batch's two-deep pipeline
   cudaEvent_t batch_ev[2] = {nullptr, nullptr};
+  // set while nrf_render_batch pipelines frames on several devices: the event after which device 0's frame may be
+  // overwritten (its copy to the staging buffer has finished); the other devices' pixel-writing composite waits on it
+  cudaEvent_t pixel_wait = nullptr;
   size_t batch_bytes = 0;
   nrf_stats stats{};
   // a frame that was enqueued without a host sync (its sample total is still unchecked against the buffer capacity)
@@ -275,8 +298,10 @@ extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&D.stream, cudaStreamNonBlocking);
     for (int k = 0; k < 6 && e == cudaSuccess; ++k) e = cudaEventCreate(&D.ev[k]);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&D.done, cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaMallocHost(&D.total_h, 16 * sizeof(unsigned long long));
-    if (e == cudaSuccess) std::memset(D.total_h, 0, 16 * sizeof(unsigned long long));
+    for (int r = 1; r < NRF_MAX_ROUNDS && e == cudaSuccess; ++r)
+      for (int k = 0; k < 4 && e == cudaSuccess; ++k) e = cudaEventCreate(&D.rev[r][k]);
+    if (e == cudaSuccess) e = cudaMallocHost(&D.total_h, 4 * TOT_N * sizeof(unsigned long long));
+    if (e == cudaSuccess) std::memset(D.total_h, 0, 4 * TOT_N * sizeof(unsigned long long));
     cudaDeviceProp prop;
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, D.dev);
     if (e != cudaSuccess) {
@@ -300,6 +325,8 @@ static void free_device(Device& D) {
   D.depth_f32.release(); D.counts.release(); D.warp_base.release(); D.block_sums.release();
   D.sample_ray.release(); D.used.release(); D.sample_out.release(); D.rgb_u8.release(); D.depth_u8.release();
   D.total.release(); D.enc.release(); D.idx.release(); D.dbg.release();
+  D.ray_state.release(); D.dead.release(); D.t_resume.release();
+  for (int r = 1; r < NRF_MAX_ROUNDS; ++r) for (int k = 0; k < 4; ++k) if (D.rev[r][k]) cudaEventDestroy(D.rev[r][k]);
   if (D.total_h) cudaFreeHost(D.total_h);
   for (int k = 0; k < 6; ++k) if (D.ev[k]) cudaEventDestroy(D.ev[k]);
   if (D.done) cudaEventDestroy(D.done);
@@ -541,8 +568,9 @@ extern "C" int nrf_set_resolution(nrf_ctx* c, int W, int H) {
     const size_t nb = (N + 127) / 128;
     CU(D.rays.ensure(N)); CU(D.ray_sh.ensure(2 * N)); CU(D.far_tf.ensure(N)); CU(D.counts.ensure(N)); CU(D.warp_base.ensure((N + 31) / 32));
     CU(D.block_sums.ensure(nb)); CU(D.used.ensure(N)); CU(D.rgb_f32.ensure(N * 3)); CU(D.depth_f32.ensure(N));
-    CU(D.total.ensure(4));
-    CU(cudaMemsetAsync(D.total.p, 0, 4 * sizeof(unsigned long long), D.stream));
+    CU(D.total.ensure(TOT_N));
+    CU(cudaMemsetAsync(D.total.p, 0, TOT_N * sizeof(unsigned long long), D.stream));
+    CU(D.ray_state.ensure(2 * N)); CU(D.dead.ensure(N)); CU(D.t_resume.ensure(N));
     if (c->use_tcache) CU(D.tcache.ensure(((N + 31) / 32) * 32 * NRF_TCACHE));
     // u8 outputs: whole-frame contexts keep ONE frame in pixel order on device 0; a sharded context keeps its packed tiles
     if (g == 0) {
@@ -650,39 +678,62 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
   }
   const size_t cap = std::min<size_t>(frame_capacity(D), (1ull << 31) - 256);
   const SampleSrc src = sample_src(D);
+  // round schedule of this frame: whole rays, or the termination-aware windows (nrf_ctx::round_bounds)
+  int bounds[NRF_MAX_ROUNDS] = {NRF_MAX_STEPS_D};
+  int n_rounds = 1;
+  if (c->chunked) {
+    n_rounds = c->n_round_bounds;
+    for (int r = 0; r < n_rounds; ++r) bounds[r] = c->round_bounds[r];
+  }
+  D.rounds_timed = n_rounds;
+  Device& D0 = c->devs[0];
+  uint8_t* rgb_dst = c->peer_frame ? peer_slot_ptr(c) : D0.rgb_u8.p;
+  uint8_t* dep_dst = c->peer_frame ? peer_slot_ptr(c) + (size_t)c->W * c->H * 3 : D0.depth_u8.p;
+  const int u8_pixel_order = (c->n_shards == 1 || c->peer_frame) ? 1 : 0;
   CU(cudaEventRecord(D.ev[0], D.stream));
-  if (D.n_local > 0) {
-    // experiment knob: unused dynamic shared memory caps the resident blocks per SM (registers allow 10)
-    static const int count_dyn_smem = std::getenv("NRF_COUNT_DYN_SMEM") ? std::atoi(std::getenv("NRF_COUNT_DYN_SMEM")) : 0;
-    k_rays_count<<<nb, 128, count_dyn_smem, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
-                                          D.ray_sh.p, D.tcache.p);
+  // this frame's counters: marched / evaluated / used / overflow flag
+  CU(cudaMemsetAsync(D.total.p + TOT_MARCHED, 0, 4 * sizeof(unsigned long long), D.stream));
+  for (int r = 0; r < n_rounds; ++r) {
+    const int s0 = r == 0 ? 0 : bounds[r - 1], s1 = bounds[r];
+    RoundWin R{s0, s1, r == 0, r == n_rounds - 1, n_rounds > 1 ? D.ray_state.p : nullptr, n_rounds > 1 ? D.dead.p : nullptr};
+    if (r > 0) CU(cudaEventRecord(D.rev[r][0], D.stream));
+    if (D.n_local > 0) {
+      if (r == 0) {
+        // experiment knob: unused dynamic shared memory caps the resident blocks per SM (registers allow 10)
+        static const int count_dyn_smem = std::getenv("NRF_COUNT_DYN_SMEM") ? std::atoi(std::getenv("NRF_COUNT_DYN_SMEM")) : 0;
+        k_rays_count<<<nb, 128, count_dyn_smem, D.stream>>>(D.march, D.map, D.n_local, D.rays.p, D.far_tf.p, D.counts.p,
+                                                            D.block_sums.p, D.ray_sh.p, D.tcache.p, s1, D.total.p + TOT_MARCHED);
+      } else {
+        k_round_sums<<<nb, 128, 0, D.stream>>>(D.n_local, D.counts.p, D.dead.p, s0, s1, D.block_sums.p);
+      }
+      CU(cudaGetLastError());
+    }
+    k_scan_blocks<<<1, 1024, 0, D.stream>>>(D.block_sums.p, D.n_local > 0 ? nb : 0, D.total.p, (unsigned long long)cap);
     CU(cudaGetLastError());
+    if (r == 0) CU(cudaEventRecord(D.ev[1], D.stream));
+    if (D.n_local > 0) {
+      k_emit<<<nb, 128, 0, D.stream>>>(D.march, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
+                                      D.warp_base.p, D.samples.p, nullptr, nullptr, nullptr, nullptr,
+                                      (long long)cap, D.tcache.p, D.t0rec.p, s0, s1, r == 0 ? nullptr : D.dead.p,
+                                      n_rounds > 1 ? D.t_resume.p : nullptr);
+      CU(cudaGetLastError());
+    }
+    CU(cudaEventRecord(r == 0 ? D.ev[2] : D.rev[r][1], D.stream));
+    CU(nrf_launch_network(2, network_grid(c, D, (int)cap), D.stream, &D.net, (int)cap, D.samples.p, nullptr, D.rays.p,
+                          D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr, D.total.p + TOT_ROUND, &src));
+    CU(cudaEventRecord(r == 0 ? D.ev[3] : D.rev[r][2], D.stream));
+    if (D.n_local > 0) {
+      // peer stores into device 0's frame must not overtake the copy-out of the previous frame (nrf_render_batch)
+      if (R.last && c->pixel_wait && &D != &D0) CU(cudaStreamWaitEvent(D.stream, c->pixel_wait, 0));
+      k_composite<<<nb, 128, 0, D.stream>>>(D.n_local, D.map, D.warp_base.p, D.counts.p, D.rays.p, D.far_tf.p, src,
+                                            D.sample_out.p, D.rgb_f32.p, D.depth_f32.p, D.used.p, rgb_dst, dep_dst,
+                                            u8_pixel_order, R, D.total.p + TOT_USED);
+      CU(cudaGetLastError());
+    }
+    CU(cudaEventRecord(r == 0 ? D.ev[4] : D.rev[r][3], D.stream));
   }
-  k_scan_blocks<<<1, 1024, 0, D.stream>>>(D.block_sums.p, D.n_local > 0 ? nb : 0, D.total.p, (unsigned long long)cap);
-  CU(cudaGetLastError());
-  CU(cudaEventRecord(D.ev[1], D.stream));
   ++D.frame_no;
-  CU(cudaMemcpyAsync(D.total_h + 4 * (D.frame_no & 3u), D.total.p, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, D.stream));
-  if (D.n_local > 0) {
-    k_emit<<<nb, 128, 0, D.stream>>>(D.march, D.n_local, D.rays.p, D.far_tf.p, D.counts.p, D.block_sums.p,
-                                    D.warp_base.p, D.samples.p, nullptr, nullptr, nullptr, nullptr,
-                                    (long long)cap, D.tcache.p, D.t0rec.p);
-    CU(cudaGetLastError());
-  }
-  CU(cudaEventRecord(D.ev[2], D.stream));
-  CU(nrf_launch_network(2, network_grid(c, D, (int)cap), D.stream, &D.net, (int)cap, D.samples.p, nullptr, D.rays.p,
-                        D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr, D.total.p, &src));
-  CU(cudaEventRecord(D.ev[3], D.stream));
-  if (D.n_local > 0) {
-    Device& D0 = c->devs[0];
-    k_composite<<<nb, 128, 0, D.stream>>>(D.n_local, D.map, D.warp_base.p, D.counts.p, D.rays.p, D.far_tf.p, src,
-                                          D.sample_out.p, D.rgb_f32.p, D.depth_f32.p, D.used.p,
-                                          c->peer_frame ? peer_slot_ptr(c) : D0.rgb_u8.p,
-                                          c->peer_frame ? peer_slot_ptr(c) + (size_t)c->W * c->H * 3 : D0.depth_u8.p,
-                                          (c->n_shards == 1 || c->peer_frame) ? 1 : 0);
-    CU(cudaGetLastError());
-  }
-  CU(cudaEventRecord(D.ev[4], D.stream));
+  CU(cudaMemcpyAsync(D.total_h + TOT_N * (D.frame_no & 3u), D.total.p, TOT_N * sizeof(unsigned long long), cudaMemcpyDeviceToHost, D.stream));
   CU(cudaEventRecord(D.done, D.stream));
   return NRF_OK;
 }
@@ -693,18 +744,20 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
 // latest one's result is still observable, earlier frames that overflowed are counted — nrf_overflowed_frames).
 static int frame_check(nrf_ctx*, Device& D, bool& redo) {
   CU(cudaSetDevice(D.dev));
-  const unsigned long long* slot = D.total_h + 4 * (D.frame_no & 3u);
-  const unsigned long long S = slot[0], mx = slot[1];   // latest frame; largest frame since the last check
-  D.overflowed = slot[2];
-  CU(cudaMemsetAsync(D.total.p + 1, 0, sizeof(unsigned long long), D.stream));   // restart the running maximum
-  if (mx > (1ull << 31) - 256) return fail(NRF_EINVAL, "frame produces %llu samples (> 2^31)", mx);
-  D.last_samples = S;
+  const unsigned long long* slot = D.total_h + TOT_N * (D.frame_no & 3u);
+  const unsigned long long mx = slot[TOT_MAX];   // largest round of any frame since the last check
+  D.overflowed = slot[TOT_OVF_EVENTS];
+  CU(cudaMemsetAsync(D.total.p + TOT_MAX, 0, sizeof(unsigned long long), D.stream));   // restart the running maximum
+  if (mx > (1ull << 31) - 256) return fail(NRF_EINVAL, "frame produces %llu samples in one round (> 2^31)", mx);
+  D.last_samples = slot[TOT_EVAL];
+  D.last_marched = slot[TOT_MARCHED];
+  D.last_used = slot[TOT_USED];
   const size_t cap = frame_capacity(D);
   if (mx > cap) {
     const size_t want = (size_t)mx + (size_t)mx / 4;
     CU(D.samples.ensure(want)); CU(D.t0rec.ensure(want)); CU(D.sample_out.ensure(want));
   }
-  if (S > cap) redo = true;
+  if (slot[TOT_FRAME_OVF]) redo = true;   // a round of the LATEST frame did not fit
   return NRF_OK;
 }
 
@@ -741,6 +794,15 @@ static int frame_resolve(nrf_ctx* c) {
       CU(cudaStreamSynchronize(D.stream));
       int rc = frame_check(c, D, redo);
       if (rc) { c->pending = false; return rc; }
+    }
+    // termination-aware rounds, decided from the frame just validated (both counts are schedule-independent)
+    if (c->term_mode == 2) {
+      unsigned long long marched = 0, used = 0;
+      for (Device& D : c->devs) { marched += D.last_marched; used += D.last_used; }
+      if (marched > 0) {
+        if (4 * used < 3 * marched) c->chunked = true;
+        else if (10 * used > 9 * marched) c->chunked = false;
+      }
     }
     if (!redo) { c->pending = false; return NRF_OK; }
     int rc = frame_enqueue_all(c, c->pending_intr, c->pending_pose, c->pending_to_host);
@@ -783,29 +845,32 @@ extern "C" int nrf_render_frame_device(nrf_ctx* c, const float intr[4], const fl
 // copied to one of two pinned staging buffers on the same stream, and while the GPU renders frame i+1 the host copies
 // frame i-1 out of the other staging buffer into the caller's memory.  A frame whose sample total exceeded the buffers
 // (possible only while the buffers are still growing) is rendered again synchronously at the end.
-extern "C" int nrf_render_batch(nrf_ctx* c, const float intr[4], const float* poses, int n_poses, uint8_t* rgb_out) {
+extern "C" int nrf_render_batch_rgbd(nrf_ctx* c, const float intr[4], const float* poses, int n_poses, uint8_t* rgb_out,
+                                     uint8_t* depth_out) {
   if (!c || !intr || !rgb_out || n_poses < 0 || (n_poses > 0 && !poses)) return fail(NRF_EINVAL, "nrf_render_batch: bad arguments");
   int n_local = 0;
   int rc = nrf_local_rays(c, &n_local);
   if (rc) return rc;
   if (!c->loaded) return fail(NRF_ESTATE, "render_batch before reload_network_from_file");
-  const size_t frame_bytes = (c->n_shards == 1 ? (size_t)c->W * c->H : (size_t)n_local) * 3;
+  const size_t px = c->n_shards == 1 ? (size_t)c->W * c->H : (size_t)n_local;
+  const size_t frame_bytes = px * 3, stage_bytes = px * (depth_out ? 4 : 3);
   if (n_poses == 0) return NRF_OK;
   // the first frame synchronously: it sizes the sample buffers
   rc = render_common(c, intr, poses, true, true);
   if (rc) return rc;
   std::memcpy(rgb_out, c->rgb_host, frame_bytes);
+  if (depth_out) std::memcpy(depth_out, c->depth_host, px);
   if (n_poses == 1) return NRF_OK;
   Device& D0 = c->devs[0];
   CU(cudaSetDevice(D0.dev));
-  if (c->batch_bytes < frame_bytes) {
+  if (c->batch_bytes < stage_bytes) {
     for (int k = 0; k < 2; ++k) {
       if (c->batch_stage[k]) cudaFreeHost(c->batch_stage[k]);
       c->batch_stage[k] = nullptr;
-      CU(cudaMallocHost(&c->batch_stage[k], frame_bytes));
+      CU(cudaMallocHost(&c->batch_stage[k], stage_bytes));
       if (!c->batch_ev[k]) CU(cudaEventCreateWithFlags(&c->batch_ev[k], cudaEventDisableTiming));
     }
-    c->batch_bytes = frame_bytes;
+    c->batch_bytes = stage_bytes;
   }
   std::vector<int> redo;
   unsigned fno[2][8] = {};   // per staging slot: frame_no of every device when the frame was enqueued
@@ -813,21 +878,29 @@ extern "C" int nrf_render_batch(nrf_ctx* c, const float intr[4], const float* po
     const int slot = j & 1;
     CU(cudaEventSynchronize(c->batch_ev[slot]));
     bool over = false;
-    for (size_t g = 0; g < c->devs.size(); ++g) over |= c->devs[g].total_h[4 * (fno[slot][g] & 3u)] > frame_capacity(c->devs[g]);
+    for (size_t g = 0; g < c->devs.size(); ++g) over |= c->devs[g].total_h[TOT_N * (fno[slot][g] & 3u) + TOT_FRAME_OVF] != 0;
     if (over) redo.push_back(j);
-    else std::memcpy(rgb_out + (size_t)j * frame_bytes, c->batch_stage[slot], frame_bytes);
+    else {
+      std::memcpy(rgb_out + (size_t)j * frame_bytes, c->batch_stage[slot], frame_bytes);
+      if (depth_out) std::memcpy(depth_out + (size_t)j * px, c->batch_stage[slot] + frame_bytes, px);
+    }
     return NRF_OK;
   };
   for (int i = 1; i < n_poses; ++i) {
     const int slot = i & 1;
     if (i >= 3) { rc = collect(i - 2); if (rc) return rc; }   // frees this staging slot
     c->peer_slot ^= 1;
+    // frame i-1's copy out of device 0's frame (recorded in batch_ev[(i-1)&1]) must finish before another device's
+    // composite stores frame i's pixels there; frame 0 was rendered synchronously
+    c->pixel_wait = i >= 2 ? c->batch_ev[(i - 1) & 1] : nullptr;
     rc = frame_enqueue_all(c, intr, poses + (size_t)i * 16, false);
+    c->pixel_wait = nullptr;
     if (rc) return rc;
     for (size_t g = 0; g < c->devs.size() && g < 8; ++g) fno[slot][g] = c->devs[g].frame_no;
     CU(cudaSetDevice(D0.dev));
     for (size_t g = 1; g < c->devs.size(); ++g) CU(cudaStreamWaitEvent(D0.stream, c->devs[g].done, 0));
     CU(cudaMemcpyAsync(c->batch_stage[slot], D0.rgb_u8.p, frame_bytes, cudaMemcpyDeviceToHost, D0.stream));
+    if (depth_out) CU(cudaMemcpyAsync(c->batch_stage[slot] + frame_bytes, D0.depth_u8.p, px, cudaMemcpyDeviceToHost, D0.stream));
     CU(cudaEventRecord(c->batch_ev[slot], D0.stream));
     c->pending = true;
     c->pending_to_host = false;
@@ -841,8 +914,13 @@ extern "C" int nrf_render_batch(nrf_ctx* c, const float intr[4], const float* po
     rc = render_common(c, intr, poses + (size_t)j * 16, true, true);
     if (rc) return rc;
     std::memcpy(rgb_out + (size_t)j * frame_bytes, c->rgb_host, frame_bytes);
+    if (depth_out) std::memcpy(depth_out + (size_t)j * px, c->depth_host, px);
   }
   return NRF_OK;
+}
+
+extern "C" int nrf_render_batch(nrf_ctx* c, const float intr[4], const float* poses, int n_poses, uint8_t* rgb_out) {
+  return nrf_render_batch_rgbd(c, intr, poses, n_poses, rgb_out, nullptr);
 }
 
 extern "C" int nrf_get_float_frame(nrf_ctx* c, float* rgb_f32, float* depth_f32, int32_t* samples_per_ray) {
@@ -883,7 +961,6 @@ extern "C" int nrf_get_stats(nrf_ctx* c, nrf_stats* out) {
   nrf_stats s{};
   s.n_rays = (uint64_t)c->W * c->H;
   s.n_gpus = (uint32_t)c->devs.size();
-  s.n_launches = 5 * s.n_gpus;
   for (Device& D : c->devs) {
     CU(cudaSetDevice(D.dev));
     CU(cudaStreamSynchronize(D.stream));
@@ -893,11 +970,40 @@ extern "C" int nrf_get_stats(nrf_ctx* c, nrf_stats* out) {
   CU(cudaSetDevice(D0.dev));
   float ms;
   CU(cudaEventElapsedTime(&ms, D0.ev[0], D0.ev[1])); s.ms_setup = ms;   // rays + count + scan (march pass 1)
-  CU(cudaEventElapsedTime(&ms, D0.ev[1], D0.ev[2])); s.ms_march = ms;   // read-back + emit (march pass 2)
+  CU(cudaEventElapsedTime(&ms, D0.ev[1], D0.ev[2])); s.ms_march = ms;   // emit (march pass 2)
   CU(cudaEventElapsedTime(&ms, D0.ev[2], D0.ev[3])); s.ms_network = ms;
   CU(cudaEventElapsedTime(&ms, D0.ev[3], D0.ev[4])); s.ms_composite = ms;
+  for (int r = 1; r < D0.rounds_timed; ++r) {   // later rounds of a termination-aware frame: sums + scan + emit | network | composite
+    CU(cudaEventElapsedTime(&ms, D0.rev[r][0], D0.rev[r][1])); s.ms_march += ms;
+    CU(cudaEventElapsedTime(&ms, D0.rev[r][1], D0.rev[r][2])); s.ms_network += ms;
+    CU(cudaEventElapsedTime(&ms, D0.rev[r][2], D0.rev[r][3])); s.ms_composite += ms;
+  }
   CU(cudaEventElapsedTime(&ms, D0.ev[0], D0.ev[5])); s.ms_total = ms;
+  s.n_rounds = (uint32_t)D0.rounds_timed;
+  s.n_launches = (5 * s.n_rounds) * s.n_gpus;
+  for (Device& D : c->devs) { s.n_samples_marched += D.last_marched; s.n_samples_used += D.last_used; }
   *out = s;
+  return NRF_OK;
+}
+
+// Termination-aware evaluation rounds (nerf_b200_ext.h).  mode 0 = whole rays, 1 = rounds always, 2 = automatic.
+// bounds (may be NULL = keep): cumulative samples-per-ray boundaries of all rounds but the last, ascending, < 1024.
+extern "C" int nrf_set_termination(nrf_ctx* c, int mode, const int* bounds, int n_bounds) {
+  if (!c || mode < 0 || mode > 2) return fail(NRF_EINVAL, "nrf_set_termination: bad arguments");
+  if (bounds) {
+    if (n_bounds < 1 || n_bounds > NRF_MAX_ROUNDS - 1) return fail(NRF_EINVAL, "nrf_set_termination: 1..%d round boundaries", NRF_MAX_ROUNDS - 1);
+    for (int i = 0; i < n_bounds; ++i)
+      if (bounds[i] < 1 || bounds[i] >= NRF_MAX_STEPS_D || (i > 0 && bounds[i] <= bounds[i - 1]))
+        return fail(NRF_EINVAL, "nrf_set_termination: boundaries must be ascending in [1, %d)", NRF_MAX_STEPS_D);
+  }
+  { int rc = frame_resolve(c); if (rc) return rc; }
+  if (bounds) {
+    for (int i = 0; i < n_bounds; ++i) c->round_bounds[i] = bounds[i];
+    c->round_bounds[n_bounds] = NRF_MAX_STEPS_D;
+    c->n_round_bounds = n_bounds + 1;
+  }
+  c->term_mode = mode;
+  c->chunked = mode == 1;
   return NRF_OK;
 }
 
@@ -961,7 +1067,8 @@ extern "C" int nrf_probe_march(nrf_ctx* c, int n, const float rays_o[3], const f
   DevBuf<float4> r, smp; DevBuf<float2> f; DevBuf<float> ta, dbg; DevBuf<int> cnt, bs, wb, sray;
   DevBuf<unsigned long long> tot; DevBuf<long long> doff;
   const int nb = (n + 127) / 128;
-  CU(r.ensure(n)); CU(f.ensure(n)); CU(cnt.ensure(n)); CU(bs.ensure(nb)); CU(wb.ensure((n + 31) / 32)); CU(tot.ensure(4));
+  CU(r.ensure(n)); CU(f.ensure(n)); CU(cnt.ensure(n)); CU(bs.ensure(nb)); CU(wb.ensure((n + 31) / 32)); CU(tot.ensure(TOT_N));
+  CU(cudaMemsetAsync(tot.p, 0, TOT_N * sizeof(unsigned long long), D.stream));
   CU(cudaMemcpyAsync(r.p, hr.data(), (size_t)n * 16, cudaMemcpyHostToDevice, D.stream));
   CU(cudaMemcpyAsync(f.p, hf.data(), (size_t)n * 8, cudaMemcpyHostToDevice, D.stream));
   k_count_given<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p);
@@ -983,7 +1090,8 @@ extern "C" int nrf_probe_march(nrf_ctx* c, int n, const float rays_o[3], const f
       CU(doff.ensure(n));
       CU(cudaMemcpyAsync(doff.p, ho.data(), (size_t)n * 8, cudaMemcpyHostToDevice, D.stream));
       CU(smp.ensure(S)); CU(ta.ensure(S)); CU(sray.ensure(S)); CU(dbg.ensure(S * 8));
-      k_emit<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p, wb.p, smp.p, ta.p, sray.p, dbg.p, doff.p, (long long)S, nullptr, nullptr);
+      k_emit<<<nb, 128, 0, D.stream>>>(M, n, r.p, f.p, cnt.p, bs.p, wb.p, smp.p, ta.p, sray.p, dbg.p, doff.p, (long long)S, nullptr, nullptr,
+                                      0, NRF_MAX_STEPS_D, nullptr, nullptr);
       CU(cudaGetLastError());
       CU(cudaMemcpyAsync(samples, dbg.p, (size_t)S * 32, cudaMemcpyDeviceToHost, D.stream));
       CU(cudaStreamSynchronize(D.stream));
@@ -1155,10 +1263,10 @@ extern "C" int nrf_exp_encode(nrf_ctx* c, int variant, int iters, float* ms_out)
 
 // ---------------------------------------------------------------------------------------------------- memory probes
 // Roofline denominators measured on the box (kernels_probe.cu).  mode 0: streaming 16-byte reads over `window_bytes`
-// (<= L2 => L2 bandwidth, >> L2 => HBM); mode 1: one random 8-byte slot (= one 32-byte sector, own 128-byte line) per
+// split over the CTAs (>> L2 => HBM); mode 2: every CTA streams the whole window (<= L2 => L2->SM bandwidth); mode 1: one random 8-byte slot (= one 32-byte sector, own 128-byte line) per
 // lane.  *gbs = bytes REQUESTED by the threads per second / 1e9 (mode 1: 8 B per load); *gloads = loads per ns.
 extern "C" int nrf_bench_memory(nrf_ctx* c, int mode, size_t window_bytes, int iters, float* gbs, float* gloads) {
-  if (!c || !gbs || mode < 0 || mode > 1 || window_bytes < (1u << 20) || iters < 1)
+  if (!c || !gbs || mode < 0 || mode > 2 || window_bytes < (1u << 20) || iters < 1)
     return fail(NRF_EINVAL, "nrf_bench_memory: bad arguments");
   Device& D = c->devs[0];
   CU(cudaSetDevice(D.dev));
@@ -1168,7 +1276,8 @@ extern "C" int nrf_bench_memory(nrf_ctx* c, int mode, size_t window_bytes, int i
   CU(cudaMalloc(&sink, 4));
   CU(cudaMemsetAsync(buf, 0, window_bytes, D.stream));
   // work per launch: mode 0 = passes over the window (>= ~4 GB read in total), mode 1 = loads per thread
-  const int work = mode == 0 ? (int)std::max<size_t>(1, (4ull << 30) / window_bytes) : 4096;
+  const int work = mode == 0 ? (int)std::max<size_t>(1, (4ull << 30) / window_bytes)
+                   : mode == 2 ? (int)std::max<size_t>(1, (64ull << 20) / window_bytes) : 4096;   // mode 2: every CTA reads the window `work` times
   cudaEvent_t e0, e1;
   CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
   CU(nrf_launch_probe(mode, D.n_sms, D.stream, buf, window_bytes, work, sink));  // warm-up (fills L2)
@@ -1181,8 +1290,9 @@ extern "C" int nrf_bench_memory(nrf_ctx* c, int mode, size_t window_bytes, int i
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   cudaFree(buf); cudaFree(sink);
   const double s = ms * 1e-3 / iters;
-  const double loads = mode == 0 ? (double)(window_bytes / 16) * work : (double)D.n_sms * 1024.0 * work;
-  const double bytes = loads * (mode == 0 ? 16.0 : 8.0);
+  const double loads = mode == 0 ? (double)(window_bytes / 16) * work
+                       : mode == 2 ? (double)(window_bytes / 16) * work * D.n_sms : (double)D.n_sms * 1024.0 * work;
+  const double bytes = loads * (mode == 1 ? 8.0 : 16.0);
   *gbs = (float)(bytes / s / 1e9);
   if (gloads) *gloads = (float)(loads / s / 1e9);
   return NRF_OK;

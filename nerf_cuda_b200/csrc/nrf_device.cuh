@@ -68,6 +68,16 @@ struct SampleSrc {
   float dt_gamma, dt_min, dt_max;
 };
 
+// One evaluation round of a frame: the samples with step index in [s0, s1) of every ray that is still alive.  A frame
+// is one round {0, NRF_MAX_STEPS_D, first, last} unless the context runs termination-aware (nrf_api.cu round_schedule):
+// then rays whose transmittance fell below 1e-4 in one round are not marched / evaluated / composited in the next.
+struct RoundWin {
+  int s0, s1;
+  int first, last;
+  float4* st;      // per-ray accumulators carried between rounds (2 float4 per ray), null for a single round
+  uint8_t* dead;   // per-ray "terminated" flag written by k_composite, read by k_round_sums / k_emit / k_composite
+};
+
 // activation ids mirror include/nerf_b200.h
 #define ACT_NONE 0
 #define ACT_RELU 1

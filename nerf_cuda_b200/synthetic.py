@@ -147,9 +147,19 @@ class Scene:
     extra: dict = field(default_factory=dict)
 
 
-def make_scene(config="C2", seed=1337, rgb_activation=NRF_ACT_NONE, table_range=1.0) -> Scene:
+def make_opaque(params: np.ndarray, gain=48.0) -> np.ndarray:
+    """"Opaque" variant of a random-init model: the density row of the density network's output layer (W1 row 0, flat
+    offset 2048..2112) is scaled so that raw densities are O(+-10) and sigma = exp(.) is either huge or ~0 — a ray
+    terminates (T < 1e-4) at its first sample with a positive raw density, like a ray hitting a trained surface.
+    Random-init weights alone give sigma ~ 1, where nothing ever terminates."""
+    p = np.array(params, np.float32, copy=True)
+    p[2048:2048 + 64] *= np.float32(gain)
+    return p
+
+
+def make_scene(config="C2", seed=1337, rgb_activation=NRF_ACT_NONE, table_range=1.0, opaque=False) -> Scene:
     """BASELINE.json configs: C1/C2 bound 1, one cascade, T=2^19; C3/C4 bound 16, 5 cascades; C5 T=2^24;
-    'tiny' = T=2^14 for fast CPU tests."""
+    'tiny' = T=2^14 for fast CPU tests.  opaque: see make_opaque."""
     if config in ("C1", "C2"):
         d = make_desc(19, 1.0, 1, rgb_activation)
         scene = "sphere"
@@ -170,7 +180,10 @@ def make_scene(config="C2", seed=1337, rgb_activation=NRF_ACT_NONE, table_range=
         scene = "unbounded"
     else:
         raise ValueError(config)
-    return Scene(d, random_params(d, seed, table_range), occupancy_grid(d, scene), aabb_of(d), config)
+    params = random_params(d, seed, table_range)
+    if opaque:
+        params = make_opaque(params)
+    return Scene(d, params, occupancy_grid(d, scene), aabb_of(d), config + ("-opaque" if opaque else ""))
 
 
 def camera_radius(config: str) -> float:

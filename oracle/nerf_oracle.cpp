@@ -724,6 +724,18 @@ int orc_num_threads(void) {
 #endif
 }
 
+// Explicit thread count for the timed CPU legs: torch.distributed.run exports OMP_NUM_THREADS=1 to every rank, which
+// would silently time the oracle on one core (bench.py sets this to the cores the process may run on).
+int orc_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n >= 1) omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  (void)n;
+  return 1;
+#endif
+}
+
 }  // extern "C"
 
 // pcg32 stream for known-answer tests (tests/test_oracle_golden.py): n outputs after `skip` advance steps.

@@ -153,6 +153,10 @@ class Oracle:
     def num_threads(self):
         return self.l.orc_num_threads()
 
+    def set_num_threads(self, n):
+        """OpenMP threads of every later call (overrides an inherited OMP_NUM_THREADS); returns the count in effect."""
+        return self.l.orc_set_num_threads(int(n))
+
 
 def half_to_float(u16):
     return np.ascontiguousarray(u16, np.uint16).view(np.float16).astype(np.float32)

@@ -96,3 +96,45 @@ def test_testbed_writes_ppm(built_lib, tmp_path):
     assert "Process time" in res.stdout
     data = open(out + ".ppm", "rb").read()
     assert data.startswith(b"P6\n64 48\n255\n") and len(data) == len(b"P6\n64 48\n255\n") + 64 * 48 * 3
+
+
+def test_server_batch_and_depth(built_lib, tmp_path):
+    """render_server --batch N --depth: one request = N poses, the response = N x (rgb frame, depth frame), rendered
+    through the pipelined nrf_render_batch.  Every frame must equal the one-at-a-time render_frame result byte for
+    byte; --batch 0 is rejected instead of busy-looping."""
+    sc = syn.make_scene("tiny16")
+    path = str(tmp_path / "synthetic16.msgpack")
+    write_snapshot(path, sc.desc, sc.params, sc.grid, sc.aabb)
+    W, H, N = 80, 56, 4
+    intr = syn.intrinsics(W, H)
+    poses = [syn.look_at_pose(12.0, 20.0, az) for az in (10.0, 100.0, 190.0, 280.0, 300.0, 40.0, 77.0, 200.0)]
+    r = NerfRender(1)
+    r.reload_network_from_file(path)
+    r.set_resolution((W, H))
+    direct = [tuple(a.copy() for a in r.render_frame(intr, p)) for p in poses]
+    rgb_b, dep_b = r.render_batch(intr, np.stack(poses[:N]), want_depth=True)
+    for k in range(N):
+        assert np.array_equal(rgb_b[k], direct[k][0]) and np.array_equal(dep_b[k], direct[k][1])
+    r.close()
+    assert subprocess.run([os.path.join(PKG, "render_server"), "--snapshot", path, "--batch", "0"],
+                          capture_output=True, timeout=60).returncode == 2
+    port = _free_port()
+    srv = subprocess.Popen([os.path.join(PKG, "render_server"), "--snapshot", path, "--port", str(port), "--width", str(W),
+                            "--height", str(H), "--fl", str(float(intr[0])), "--cx", str(float(intr[2])), "--cy",
+                            str(float(intr[3])), "--batch", str(N), "--depth", "--max-requests", "2"],
+                           stdout=subprocess.PIPE, text=True)
+    try:
+        assert "Awaiting connections" in srv.stdout.readline()
+        sock = socket.create_connection(("127.0.0.1", port), timeout=60)
+        for req in range(2):
+            chunk = poses[req * N:(req + 1) * N]
+            sock.sendall(np.asarray(np.stack(chunk), "<f4").tobytes())
+            for k in range(N):
+                frame = np.frombuffer(_recv(sock, 3 * W * H), np.uint8).reshape(H, W, 3)
+                depth = np.frombuffer(_recv(sock, W * H), np.uint8).reshape(H, W)
+                assert np.array_equal(frame, direct[req * N + k][0]) and np.array_equal(depth, direct[req * N + k][1])
+        sock.close()
+        assert srv.wait(timeout=30) == 0
+    finally:
+        if srv.poll() is None:
+            srv.kill()
