@@ -43,6 +43,16 @@ namespace ngp { using tcnn::parallel_for_gpu; }
 
 using namespace ngp;
 
+// The per-level grid scale exactly as tcnn's kernel_grid evaluates it on the device (grid.h:159,186: `level` is a
+// uint32_t, scale = exp2f(level * log2_per_level_scale) * base_resolution - 1.0f), compiled with the same nvcc defaults.
+// The reference never exposes this value; the oracle needs it because MUFU.EX2 cannot be reproduced on the host.
+__global__ void ref_level_scales(uint32_t n_levels, uint32_t base_resolution, float log2_per_level_scale, float* out) {
+  const uint32_t level = threadIdx.x;
+  if (level >= n_levels) return;
+  const float scale = exp2f(level * log2_per_level_scale) * base_resolution - 1.0f;
+  out[level] = scale;
+}
+
 static void write_file(const std::string& path, const void* p, size_t bytes) {
   FILE* f = fopen(path.c_str(), "wb");
   if (!f) { fprintf(stderr, "cannot write %s\n", path.c_str()); exit(2); }
@@ -71,6 +81,21 @@ int main(int argc, char** argv) {
   render->reload_network_from_file(snapshot);
   double load_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   printf("{\"event\": \"loaded\", \"seconds\": %.3f, \"n_params\": %zu}\n", load_s, render->m_nerf_network[0]->n_params());
+  {
+    // encoding parameters as reset_network derives them (nerf_render.cu:125-170)
+    const json& enc = render->m_network_config["encoding"];
+    const uint32_t n_levels = enc.value("n_levels", 16u), log2_hashmap_size = enc.value("log2_hashmap_size", 15);
+    uint32_t base = enc.value("base_resolution", 0);
+    if (!base) base = 1u << (log2_hashmap_size / 3);
+    float pls = enc.value("per_level_scale", 0.0f);
+    if (pls <= 0.0f && n_levels > 1) pls = std::exp(std::log(2048.0f * (float)render->m_bound / (float)base) / (n_levels - 1));
+    tcnn::GPUMemory<float> d_scales(n_levels);
+    ref_level_scales<<<1, 32>>>(n_levels, base, std::log2(pls), d_scales.data());
+    std::vector<float> h(n_levels);
+    d_scales.copy_to_host(h);
+    write_file(out + "/level_scales.f32", h.data(), h.size() * 4);
+    printf("{\"event\": \"level_scales\", \"n_levels\": %u, \"base_resolution\": %u, \"per_level_scale\": %.9g}\n", n_levels, base, pls);
+  }
   int a = 3;
   while (a < argc) {
     const std::string mode = argv[a++];

@@ -119,6 +119,8 @@ def golden(out_dir):
                 march_xyz=mx[:, :keep].astype(np.float32), march_deltas=md[:, :keep].astype(np.float32),
                 march_nears=np.fromfile(os.path.join(tmp, "march_nears.f32"), np.float32),
                 march_fars=np.fromfile(os.path.join(tmp, "march_fars.f32"), np.float32),
+                march_rays_d=np.ascontiguousarray(np.fromfile(os.path.join(tmp, "march_rays_d.f32"), np.float32).reshape(3, n32).T),
+                level_scales=np.fromfile(os.path.join(tmp, "level_scales.f32"), np.float32),   # device exp2f (MUFU.EX2)
             )
             probes = [ln for ln in stdout.splitlines() if "Inference" in ln]
             summary[name] = {"events": ev, "test_probe_lines": probes, "max_count": int(counts.max()), "samples": int(counts.sum())}

@@ -167,6 +167,9 @@ int nrf_probe_march(nrf_ctx* ctx, int n, const float rays_o[3], const float* ray
 /* K10 (tcnn grid.h:139-268): positions n*3 in [0,1]; enc_out n*32 fp16 bit patterns (sample-major);
  * indices_out (may be NULL) n*L*8 uint32 entry indices (corner order of grid.h:239-251). */
 int nrf_probe_encode(nrf_ctx* ctx, int n, const float* positions, uint16_t* enc_out, uint32_t* indices_out);
+/* tcnn kernel_sh<__half>, degree 4 (spherical_harmonics.h:46-152): dirs n*3 in [0,1] (normalised direction input);
+ * sh_out n*16 fp16 bit patterns.  The frame path evaluates this once per ray. */
+int nrf_probe_sh(nrf_ctx* ctx, int n, const float* dirs, uint16_t* sh_out);
 /* K11-K14 (fully_fused_mlp.cu, spherical_harmonics.h, nerf_network.h:148-196): enc n*32 fp16, dirs n*3 in [0,1]
  * (normalised direction input); out n*4 float {r,g,b,sigma}.  impl: 0 = tcgen05 kernel, 1 = SIMT check kernel. */
 int nrf_probe_network(nrf_ctx* ctx, int n, const uint16_t* enc, const float* dirs, float* out, int impl);

@@ -55,6 +55,12 @@ int nrf_peer_frame_to_host(nrf_ctx* ctx, uint8_t** rgb, uint8_t** depth);
  * reference has no equivalent: it blocks on a device->host read after every <= 8 march steps (nerf_render.cu:291). */
 int nrf_overflowed_frames(nrf_ctx* ctx, uint64_t* n_frames);
 
+/* Per-level hash-grid scale[L] and resolution[L] of the loaded model AS THE DEVICE EVALUATES THEM.  The reference derives
+ * both inside kernel_grid with the device's exp2f (tcnn grid.h:186-187: exp2f(level*log2(per_level_scale))*base - 1),
+ * which differs from the host's exp2f by an ulp on some levels; nrf_level_table (host arithmetic, usable without a GPU)
+ * returns the host values, which is what the OFFSET table is built from (grid.h:899-931).  Either pointer may be NULL. */
+int nrf_get_level_scales(nrf_ctx* ctx, float* scales, uint32_t* resolutions);
+
 /* nrf_render_batch with the depth channel: depth_out (may be NULL) receives n * W*H bytes, frame after frame, the u8
  * depth of struct Image (common.h:76-89) that the reference computes but never sends (render_server.cu:101). */
 int nrf_render_batch_rgbd(nrf_ctx* ctx, const float intr[4], const float* poses_rowmajor, int n_poses, uint8_t* rgb_out,
@@ -63,7 +69,7 @@ int nrf_render_batch_rgbd(nrf_ctx* ctx, const float intr[4], const float* poses_
 /* Termination-aware evaluation.  The reference kills a ray as soon as its transmittance falls below 1e-4
  * (render_utils.h:727, rays_t = -1) and compacts it away before its next wavefront of <= 8 steps (kernel_compact_rays,
  * render_utils.h:394-415; nerf_render.cu:278-302), so samples behind an opaque surface never reach its network.  Here a
- * frame is evaluated in ROUNDS of samples per ray — by default [0,16), [16,64), [64,1024) — each round marching,
+ * frame is evaluated in ROUNDS of samples per ray — by default [0,8), [8,32), [32,128), [128,1024) — each round marching,
  * evaluating and compositing only the rays still alive, all enqueued without a host round trip.  mode 0: one round (whole
  * rays; right when almost nothing terminates, e.g. random-init weights); 1: rounds always; 2 (default): automatic — rounds
  * are switched on when the last validated frame composited < 3/4 of the samples its march found and off again above

@@ -244,9 +244,16 @@ class NerfRender:
                                        tonemap_curve, int(bool(clamp)), _p(out, C.c_float)))
         return accum, out
 
+    def level_scales(self):
+        """Per-level grid scales as the device evaluates them (nerf_b200_ext.h nrf_get_level_scales): what the oracle's
+        "cuda" numerics need, since MUFU.EX2 cannot be reproduced on the host."""
+        sc = np.zeros(16, np.float32)
+        _check(self._l.nrf_get_level_scales(self._ctx, _p(sc, C.c_float), None))
+        return sc
+
     def set_termination(self, mode=2, bounds=None):
         """Termination-aware evaluation rounds (nerf_b200_ext.h nrf_set_termination): mode 0 whole rays, 1 rounds,
-        2 automatic; bounds = cumulative per-ray sample boundaries of all rounds but the last (default 16, 64)."""
+        2 automatic; bounds = cumulative per-ray sample boundaries of all rounds but the last (default 8, 32, 128)."""
         b = (C.c_int * len(bounds))(*bounds) if bounds else None
         _check(self._l.nrf_set_termination(self._ctx, int(mode), b, len(bounds) if bounds else 0))
 
@@ -294,6 +301,13 @@ class NerfRender:
         idx = np.zeros((n, 16, 8), np.uint32) if want_indices else None
         _check(self._l.nrf_probe_encode(self._ctx, n, _p(positions, C.c_float), _p(enc, C.c_uint16), _p(idx, C.c_uint32)))
         return (enc, idx) if want_indices else enc
+
+    def probe_sh(self, dirs01):
+        dirs01 = _f32(dirs01)
+        n = dirs01.shape[0]
+        out = np.zeros((n, 16), np.uint16)
+        _check(self._l.nrf_probe_sh(self._ctx, n, _p(dirs01, C.c_float), _p(out, C.c_uint16)))
+        return out
 
     def probe_network(self, enc_u16, dirs01, impl=0):
         enc_u16, dirs01 = np.ascontiguousarray(enc_u16, np.uint16), _f32(dirs01)

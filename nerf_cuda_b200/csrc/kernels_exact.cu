@@ -1,8 +1,11 @@
 // kernels_exact.cu — ray setup, occupancy march (count + emit) and the occupancy bitfield builder.
 //
-// This translation unit is compiled with -fmad=false: every expression below is evaluated exactly as the
-// reference writes it (no FMA contraction, IEEE div/sqrt) so that ray directions, near/far, sample positions,
-// step sizes and sample counts are BIT-EXACT against the oracle (oracle/nerf_oracle.cpp, -ffp-contract=off).
+// Numerics: ray directions, near/far, sample positions, step sizes and sample counts are BIT-EXACT against the
+// reference's CUDA build executed on a B200 (tests/golden/ref_cuda_*.npz) and against the oracle in its "cuda" mode.
+// The reference is compiled with nvcc's default -fmad=true, so its kernels contract a*b+c into one FFMA wherever the
+// compiler chose to; this translation unit is compiled with -fmad=false (nothing is contracted implicitly, IEEE
+// div/sqrt) and every fused multiply-add of the reference's sm_100 SASS is written out as an explicit __fmaf_rn:
+// set_rays_d (norm, R*v), kernel_march_rays (o + t*d, x*rb + 1, (.)*mip_bound - x), linear_transformer (w*x + b).
 //
 // Replaces the reference kernels K1-K7 of SURVEY.md §2c:
 //   set_rays_o/set_rays_d (include/nerf-cuda/render_utils.h:31-66), kernel_near_far_from_aabb (:338-392),
@@ -32,10 +35,12 @@ __device__ __forceinline__ void ray_dir(const MarchParams& P, int p, float d[3])
   const float xs = (i - P.intr[2]) / P.intr[0] * 1.0f;
   const float ys = (j - P.intr[3]) / P.intr[1] * 1.0f;
   const float zs = 1.0f;
-  const float nrm = sqrtf(xs * xs + (ys * ys + zs * zs));  // Eigen fixed-size-3 reduction order
+  // Eigen fixed-size-3 reduction order a0 + (a1 + a2); reference SASS: FFMA(ys,ys,1), FFMA(xs,xs,.) and per row
+  // FMUL(vy,R1), FFMA(vz,R2,.), FFMA(vx,R0,.)
+  const float nrm = sqrtf(__fmaf_rn(xs, xs, __fmaf_rn(ys, ys, zs * zs)));
   const float v0 = xs / nrm, v1 = ys / nrm, v2 = zs / nrm;
 #pragma unroll
-  for (int r = 0; r < 3; ++r) d[r] = P.R[r * 3 + 0] * v0 + (P.R[r * 3 + 1] * v1 + P.R[r * 3 + 2] * v2);
+  for (int r = 0; r < 3; ++r) d[r] = __fmaf_rn(P.R[r * 3 + 0], v0, __fmaf_rn(P.R[r * 3 + 2], v2, P.R[r * 3 + 1] * v1));
 }
 
 __device__ __forceinline__ void near_far(const MarchParams& P, const float d[3], float& near_o, float& far_o) {
@@ -128,7 +133,8 @@ __device__ __noinline__ float4 clamp_to_box(float bound, float x, float y, float
 
 template <bool FAST>
 __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R, float& t, Step& s) {
-  float x = R.o[0] + t * R.d[0], y = R.o[1] + t * R.d[1], z = R.o[2] + t * R.d[2];
+  // reference SASS: FFMA(d, t, o)
+  float x = __fmaf_rn(t, R.d[0], R.o[0]), y = __fmaf_rn(t, R.d[1], R.o[1]), z = __fmaf_rn(t, R.d[2], R.o[2]);
   float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
   if (FAST) {
     if (mx > R.bound) { const float4 c = clamp_to_box(R.bound, x, y, z); x = c.x; y = c.y; z = c.z; mx = c.w; }
@@ -157,9 +163,9 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
     ny = (int)fminf(__fmaf_rn(y, mip_rbound, 1.0f) * halfH, hm1);
     nz = (int)fminf(__fmaf_rn(z, mip_rbound, 1.0f) * halfH, hm1);
   } else {
-    nx = (int)clampf((x * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
-    ny = (int)clampf((y * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
-    nz = (int)clampf((z * mip_rbound + 1.0f) * halfH, 0.0f, hm1);
+    nx = (int)clampf(__fmaf_rn(x, mip_rbound, 1.0f) * halfH, 0.0f, hm1);   // reference SASS: FFMA(x, rb, 1), DMUL x2
+    ny = (int)clampf(__fmaf_rn(y, mip_rbound, 1.0f) * halfH, 0.0f, hm1);
+    nz = (int)clampf(__fmaf_rn(z, mip_rbound, 1.0f) * halfH, 0.0f, hm1);
   }
   const uint32_t cell = ((level * H + nx) * H + ny) * H + nz;
   uint32_t occ_u;  // ((word >> (cell & 31)) & 1) != 0, kept opaque: SHF + predicate-writing LOP3 (2 issue slots, not 3)
@@ -182,9 +188,9 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
     ty = __fmaf_rn(qy, mip_bound, -y) * R.rd[1];
     tz = __fmaf_rn(qz, mip_bound, -z) * R.rd[2];
   } else {
-    tx = ((qx * 2.0f - 1.0f) * mip_bound - x) * R.rd[0];
-    ty = ((qy * 2.0f - 1.0f) * mip_bound - y) * R.rd[1];
-    tz = ((qz * 2.0f - 1.0f) * mip_bound - z) * R.rd[2];
+    tx = __fmaf_rn(qx * 2.0f - 1.0f, mip_bound, -x) * R.rd[0];   // reference SASS: FFMA(q,2,-1) [exact], FFMA(.,mip_bound,-x)
+    ty = __fmaf_rn(qy * 2.0f - 1.0f, mip_bound, -y) * R.rd[1];
+    tz = __fmaf_rn(qz * 2.0f - 1.0f, mip_bound, -z) * R.rd[2];
   }
   const float tt = t + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
   // tt >= t (the increment is max(0, .), and max(0, NaN) = 0), so every t the loop multiplies lies in [t, tt]
@@ -468,17 +474,17 @@ k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ 
       for (int j = 0; j < EMIT_CHUNK; ++j) {
         if (c < nrep) {
           const float t0 = tq[j];
-          const float x = clampf(R.o[0] + t0 * R.d[0], -R.bound, R.bound);
-          const float y = clampf(R.o[1] + t0 * R.d[1], -R.bound, R.bound);
-          const float z = clampf(R.o[2] + t0 * R.d[2], -R.bound, R.bound);
+          const float x = clampf(__fmaf_rn(t0, R.d[0], R.o[0]), -R.bound, R.bound);
+          const float y = clampf(__fmaf_rn(t0, R.d[1], R.o[1]), -R.bound, R.bound);
+          const float z = clampf(__fmaf_rn(t0, R.d[2], R.o[2]), -R.bound, R.bound);
           const float dt = clampf(t0 * R.dt_gamma, R.dt_min, R.dt_max);
           t = t0 + dt;
           const long long k = off + __popc(alive & lt);
           if (t_rec) {   // frame path (SampleSrc): ray index in the fourth component, the sample's t beside it
-            samples[k] = make_float4(P.pos_w * x + 0.5f, P.pos_w * y + 0.5f, P.pos_w * z + 0.5f, __int_as_float(q));
+            samples[k] = make_float4(__fmaf_rn(P.pos_w, x, 0.5f), __fmaf_rn(P.pos_w, y, 0.5f), __fmaf_rn(P.pos_w, z, 0.5f), __int_as_float(q));
             t_rec[k] = t0;
           } else {
-            samples[k] = make_float4(P.pos_w * x + 0.5f, P.pos_w * y + 0.5f, P.pos_w * z + 0.5f, dt);
+            samples[k] = make_float4(__fmaf_rn(P.pos_w, x, 0.5f), __fmaf_rn(P.pos_w, y, 0.5f), __fmaf_rn(P.pos_w, z, 0.5f), dt);
             t_after[k] = t;
             sample_ray[k] = q;
           }
@@ -494,10 +500,10 @@ k_emit(const __grid_constant__ MarchParams P, int n, const float4* __restrict__ 
     if (!(fast ? march_step<true>(P, R, t, s) : march_step<false>(P, R, t, s))) continue;
     const long long k = off + __popc(alive & lt);
     if (t_rec) {
-      samples[k] = make_float4(P.pos_w * s.x + 0.5f, P.pos_w * s.y + 0.5f, P.pos_w * s.z + 0.5f, __int_as_float(q));
+      samples[k] = make_float4(__fmaf_rn(P.pos_w, s.x, 0.5f), __fmaf_rn(P.pos_w, s.y, 0.5f), __fmaf_rn(P.pos_w, s.z, 0.5f), __int_as_float(q));
       t_rec[k] = t0;
     } else {
-      samples[k] = make_float4(P.pos_w * s.x + 0.5f, P.pos_w * s.y + 0.5f, P.pos_w * s.z + 0.5f, s.dt);
+      samples[k] = make_float4(__fmaf_rn(P.pos_w, s.x, 0.5f), __fmaf_rn(P.pos_w, s.y, 0.5f), __fmaf_rn(P.pos_w, s.z, 0.5f), s.dt);
       t_after[k] = t;
       sample_ray[k] = q;
     }

@@ -25,8 +25,11 @@
 // The 8 groups of a CTA walk ONE contiguous chunk of tiles interleaved (tile = chunk + 8*j + g): at any time an SM works
 // on neighbouring patches / steps of the warp-interleaved sample list, which is what the L1 hit rate lives on.
 //
-// Numerics: hash indices and fp16 interpolation follow the reference bit-exactly (this TU is built with -fmad=false);
-// the MLP accumulates in fp32 (TMEM) and rounds to fp16 at each layer boundary like the oracle.
+// Numerics: hash indices and fp16 interpolation are bit-exact against the reference's CUDA build executed on a B200
+// (tests/golden/ref_cuda_*.npz): the per-level scale comes from the device's exp2f (k_level_scales below), the position
+// is one FFMA like in the reference's SASS, everything else is uncontracted (this TU is built with -fmad=false);
+// the MLP accumulates in fp32 (TMEM) and rounds to fp16 at each layer boundary like the oracle (the reference
+// accumulates in fp16 inside wmma: outputs agree to ~5e-4 absolute, tests/test_ref_cuda_golden.py).
 #include <cstdlib>
 
 #include "nrf_device.cuh"
@@ -158,7 +161,8 @@ struct LevelTaps {
 
 template <bool IDX>
 __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float u1, float u2, LevelTaps& T, uint32_t* idx_out) {
-  const float p0 = u0 * lv.scale + 0.5f, p1 = u1 * lv.scale + 0.5f, p2 = u2 * lv.scale + 0.5f;  // -fmad=false
+  // pos_fract (common_device.h:424-431): input*scale + 0.5 is ONE FFMA in the reference's kernel_grid SASS
+  const float p0 = __fmaf_rn(u0, lv.scale, 0.5f), p1 = __fmaf_rn(u1, lv.scale, 0.5f), p2 = __fmaf_rn(u2, lv.scale, 0.5f);
   const float f0 = floorf(p0), f1 = floorf(p1), f2 = floorf(p2);
   const uint32_t g0 = (uint32_t)(int)f0, g1 = (uint32_t)(int)f1, g2 = (uint32_t)(int)f2;
   T.w0 = p0 - f0; T.w1 = p1 - f1; T.w2 = p2 - f2;
@@ -549,6 +553,29 @@ k_network_simt(const __grid_constant__ NetParams P, int n, const uint4* __restri
   dense_simt(W + 9216, 16, 64, h2, o16, false);
   out[i] = make_uint2(pack_h2(act_h(P.rgb_act, o16[0]), act_h(P.rgb_act, o16[1])),
                       pack_h2(act_h(P.rgb_act, o16[2]), sigma));
+}
+
+// Load-time: per-level scale and resolution exactly as the reference's kernel_grid derives them ON THE DEVICE
+// (grid.h:186-187): scale = exp2f(level * log2_per_level_scale) * base_resolution - 1 (FMUL, MUFU.EX2, FFMA in its SASS),
+// resolution = (uint32_t)ceil(scale) + 1.  The host's exp2f differs from MUFU.EX2 by an ulp on some levels.
+extern "C" __global__ void k_level_scales(int n_levels, float log2_per_level_scale, uint32_t base_resolution,
+                                          float* __restrict__ scales, uint32_t* __restrict__ resolutions) {
+  const int level = threadIdx.x;
+  if (level >= n_levels) return;
+  const float scale = __fmaf_rn(exp2f((float)level * log2_per_level_scale), (float)base_resolution, -1.0f);
+  scales[level] = scale;
+  resolutions[level] = (uint32_t)ceilf(scale) + 1u;
+}
+
+// Stage probe (nrf_probe_sh): the 16 SH coefficients of n normalised directions, as the frame path's k_rays_count stores them.
+extern "C" __global__ void k_probe_sh(int n, const float4* __restrict__ dirs01, uint4* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 d = dirs01[i];
+  uint32_t sh[8];
+  sh4(d.x, d.y, d.z, sh);
+  out[2 * (size_t)i] = make_uint4(sh[0], sh[1], sh[2], sh[3]);
+  out[2 * (size_t)i + 1] = make_uint4(sh[4], sh[5], sh[6], sh[7]);
 }
 
 // ------------------------------------------------------------------------------------------------ host launchers

@@ -10,6 +10,7 @@
 //     into the pinned host frame (strided 2-D copy) — no CPU de-interleave loop;
 //   * there is no CPU path: without a CUDA device every compute entry point returns NRF_ENODEV.
 #include <cuda_runtime.h>
+#include <sys/stat.h>
 
 #include <algorithm>
 #include <cmath>
@@ -41,6 +42,9 @@ __global__ void k_emit(const MarchParams P, int n, const float4* rays, const flo
                        float* t_rec, int s0, int s1, const uint8_t* dead, float* t_resume);
 __global__ void k_build_occupancy(const float* grid, uint32_t n_cells, float thresh, uint32_t* bits);
 __global__ void k_cast_half(const float* in, __half* out, size_t n);
+__global__ void k_probe_sh(int n, const float4* dirs01, uint4* out);
+__global__ void k_level_scales(int n_levels, float log2_per_level_scale, uint32_t base_resolution, float* scales,
+                               uint32_t* resolutions);
 __global__ void k_accumulate(int n, const float4* frame, float4* accum, float sample_count, int color_space);
 __global__ void k_tonemap(int n, const float4* accum, float exposure, float4 background, int color_space,
                           int output_color_space, int curve, int clamp_output, float4* out);
@@ -239,14 +243,14 @@ struct Device {
 struct nrf_ctx {
   std::vector<Device> devs;
   // Evaluation rounds of a frame (cumulative step boundaries; the last is always NRF_MAX_STEPS_D).  One round = whole
-  // rays, what the headline benchmark runs.  Termination-aware: {16, 64, 1024} — rays that turned opaque in a round are
+  // rays, what the headline benchmark runs.  Termination-aware: {8, 32, 128, 1024} — rays that turned opaque in a round are
   // neither marched, evaluated nor composited in the next (the reference drops them from its next <= 8-step wavefront,
   // render_utils.h:727 + :394-415).  term_mode 0 = off, 1 = on, 2 = auto: switched on when the last validated frame
   // composited less than 3/4 of the samples its march produced, off again above 9/10.  Pixels do not depend on it.
   int term_mode = 2;
   bool chunked = false;
-  int round_bounds[NRF_MAX_ROUNDS] = {16, 64, NRF_MAX_STEPS_D, NRF_MAX_STEPS_D};
-  int n_round_bounds = 3;
+  int round_bounds[NRF_MAX_ROUNDS] = {8, 32, 128, NRF_MAX_STEPS_D};
+  int n_round_bounds = 4;
   nrf_model_desc desc{};
   HostLevels levels{};
   float aabb[6] = {};
@@ -395,6 +399,19 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
   CU(cudaMemcpyAsync(D.mlp_packed.p, packed.data(), 20480, cudaMemcpyHostToDevice, D.stream));
   CU(cudaStreamSynchronize(D.stream));
   tmp.release();
+  // per-level scale / resolution as the reference's kernel derives them on the device (grid.h:186-187); the offset
+  // table stays the host's (grid.h:899-931 runs in the GridEncoding constructor)
+  {
+    DevBuf<float> sc;
+    DevBuf<uint32_t> rs;
+    CU(sc.ensure(NRF_MAX_LEVELS)); CU(rs.ensure(NRF_MAX_LEVELS));
+    k_level_scales<<<1, 32, 0, D.stream>>>((int)d.n_levels, std::log2(c->levels.per_level_scale), c->desc.base_resolution, sc.p, rs.p);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(c->levels.scales, sc.p, d.n_levels * sizeof(float), cudaMemcpyDeviceToHost, D.stream));
+    CU(cudaMemcpyAsync(c->levels.res, rs.p, d.n_levels * sizeof(uint32_t), cudaMemcpyDeviceToHost, D.stream));
+    CU(cudaStreamSynchronize(D.stream));
+    sc.release(); rs.release();
+  }
   // parameter blocks
   NetParams& N = D.net;
   for (uint32_t l = 0; l < d.n_levels; ++l) {
@@ -470,25 +487,22 @@ extern "C" int nrf_load_raw(nrf_ctx* c, const nrf_model_desc* desc, const float*
   return NRF_OK;
 }
 
-// Reads and parses a snapshot file on the host (no device needed).
+// Reads and parses a snapshot file on the host (no device needed); uses / refreshes the binary side-cache.
 static int read_snapshot(const char* path, nrf::Snapshot& snap) {
   const std::string p(path);
   // reload_network_from_file accepts only .msgpack (nerf_render.cu:98,105-107)
-  if (p.size() < 8 || p.substr(p.size() - 8) != ".msgpack")
-    return fail(NRF_EIO, "Network config %s must be a .msgpack snapshot.", path);
-  FILE* f = std::fopen(path, "rb");
-  if (!f) return fail(NRF_EIO, "Network config %s does not exist.", path);  // nerf_render.cu:73-76
-  std::fseek(f, 0, SEEK_END);
-  const long sz = std::ftell(f);
-  std::fseek(f, 0, SEEK_SET);
-  std::vector<uint8_t> buf((size_t)std::max(0L, sz));
-  const size_t got = sz > 0 ? std::fread(buf.data(), 1, (size_t)sz, f) : 0;
-  std::fclose(f);
-  if ((long)got != sz) return fail(NRF_EIO, "short read on %s", path);
+  if (!nrf::has_ext(p, "msgpack")) return fail(NRF_EIO, "Network config %s must be a .msgpack snapshot.", path);
   try {
+    struct stat st;
+    if (::stat(path, &st) != 0) return fail(NRF_EIO, "Network config %s does not exist.", path);  // nerf_render.cu:73-76
+    const bool use_cache = nrf::cache_enabled((size_t)st.st_size);
+    if (use_cache && nrf::cache_load(p, snap)) return NRF_OK;
+    const std::vector<uint8_t> buf = nrf::read_file(p);
     nrf::parse_snapshot(buf.data(), buf.size(), p, snap);
+    if (use_cache) nrf::cache_store(p, snap);
   } catch (const std::exception& e) {
-    return fail(NRF_EFORMAT, "%s", e.what());
+    const bool missing = std::strstr(e.what(), "does not exist") != nullptr;
+    return fail(missing ? NRF_EIO : NRF_EFORMAT, "%s", e.what());
   }
   return NRF_OK;
 }
@@ -505,6 +519,26 @@ extern "C" int nrf_load_snapshot(nrf_ctx* c, const char* path) {
 extern "C" int nrf_snapshot_inspect(const char* path, nrf_model_desc* desc, uint64_t* n_params, uint64_t* n_grid,
                                     float aabb[6], double* params_sum, double* grid_sum) {
   if (!path) return fail(NRF_EINVAL, "nrf_snapshot_inspect: null path");
+  const std::string p(path);
+  if (nrf::has_ext(p, "json")) {
+    // load_network_config's .json branch (nerf_render.cu:79-82): comments allowed, "parent" chain merged (RFC 7386).
+    // A .json config carries no weights: the array outputs are zero.
+    try {
+      const nrf::Val cfg = nrf::load_json_config(p);
+      nrf_model_desc d;
+      nrf::describe_model(cfg, d);
+      if (desc) *desc = d;
+    } catch (const std::exception& e) {
+      const bool missing = std::strstr(e.what(), "does not exist") != nullptr;
+      return fail(missing ? NRF_EIO : NRF_EFORMAT, "%s", e.what());
+    }
+    if (n_params) *n_params = 0;
+    if (n_grid) *n_grid = 0;
+    if (aabb) std::memset(aabb, 0, 24);
+    if (params_sum) *params_sum = 0;
+    if (grid_sum) *grid_sum = 0;
+    return NRF_OK;
+  }
   nrf::Snapshot snap;
   int rc = read_snapshot(path, snap);
   if (rc) return rc;
@@ -514,6 +548,17 @@ extern "C" int nrf_snapshot_inspect(const char* path, nrf_model_desc* desc, uint
   if (aabb) std::memcpy(aabb, snap.aabb, 24);
   if (params_sum) { double s = 0; for (float v : snap.params) s += v; *params_sum = s; }
   if (grid_sum) { double s = 0; for (float v : snap.density_grid) s += v; *grid_sum = s; }
+  return NRF_OK;
+}
+
+// Per-level grid scale and resolution of the loaded model as evaluated on the device (see upload_model).
+extern "C" int nrf_get_level_scales(nrf_ctx* c, float* scales, uint32_t* resolutions) {
+  if (!c) return fail(NRF_EINVAL, "null ctx");
+  if (!c->loaded) return fail(NRF_ESTATE, "no model loaded");
+  for (uint32_t l = 0; l < c->desc.n_levels; ++l) {
+    if (scales) scales[l] = c->levels.scales[l];
+    if (resolutions) resolutions[l] = c->levels.res[l];
+  }
   return NRF_OK;
 }
 
@@ -1139,6 +1184,23 @@ extern "C" int nrf_probe_encode(nrf_ctx* c, int n, const float* positions, uint1
   if (indices_out) CU(cudaMemcpyAsync(indices_out, D.idx.p, (size_t)n * NRF_L * 8 * 4, cudaMemcpyDeviceToHost, D.stream));
   CU(cudaStreamSynchronize(D.stream));
   pos.release();
+  return NRF_OK;
+}
+
+extern "C" int nrf_probe_sh(nrf_ctx* c, int n, const float* dirs, uint16_t* sh_out) {
+  if (!c || n < 0 || (n > 0 && (!dirs || !sh_out))) return fail(NRF_EINVAL, "nrf_probe_sh: bad arguments");
+  if (n == 0) return NRF_OK;
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  DevBuf<float4> d4; DevBuf<uint4> o;
+  int rc = upload_vec3_as_float4(D, n, dirs, d4);
+  if (rc) return rc;
+  CU(o.ensure(2 * (size_t)n));
+  k_probe_sh<<<(n + 127) / 128, 128, 0, D.stream>>>(n, d4.p, o.p);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(sh_out, o.p, (size_t)n * 32, cudaMemcpyDeviceToHost, D.stream));
+  CU(cudaStreamSynchronize(D.stream));
+  d4.release(); o.release();
   return NRF_OK;
 }
 

@@ -29,7 +29,8 @@ struct LevelInfo {
   uint32_t offset;  // first entry of the level (in entries)
   uint32_t size;    // T_l entries
   uint32_t res;     // grid resolution
-  float scale;      // exp2f(l*log2(b))*N_min - 1, computed on the HOST (see DESIGN.md numerics contract)
+  float scale;      // exp2f(l*log2(b))*N_min - 1 evaluated on the DEVICE like the reference's kernel_grid does (grid.h:186;
+                    // MUFU.EX2 and glibc's exp2f differ by an ulp on some levels), once at load time (k_level_scales)
   uint32_t hashed;  // 1 if res^3 > T_l (fast_hash), 0 = dense index
   uint32_t pad;
   const uint32_t* tab;  // first entry of the level (one __half2 = one uint32 per entry): address = tab + index, 1 IMAD.WIDE
@@ -104,16 +105,18 @@ __device__ __forceinline__ void sh4(float i0, float i1, float i2, uint32_t out[8
   v[3] = -0.48860251190291987f * x;
   v[4] = 1.0925484305920792f * xy;
   v[5] = -1.0925484305920792f * yz;
-  v[6] = 0.94617469575755997f * z2 - 0.31539156525251999f;
+  // the fused multiply-adds are those of the reference's kernel_sh<__half> SASS (nvcc -fmad=true): entries 6, 8, 9, 11,
+  // 12, 13, 15; everything else is a plain product (the TUs that include this are compiled with -fmad=false)
+  v[6] = __fmaf_rn(0.94617469575755997f, z2, -0.31539156525251999f);
   v[7] = -1.0925484305920792f * xz;
-  v[8] = 0.54627421529603959f * x2 - 0.54627421529603959f * y2;
-  v[9] = 0.59004358992664352f * y * (-3.0f * x2 + y2);
+  v[8] = __fmaf_rn(0.54627421529603959f, x2, -(0.54627421529603959f * y2));
+  v[9] = 0.59004358992664352f * y * __fmaf_rn(-3.0f, x2, y2);
   v[10] = 2.8906114426405538f * xy * z;
-  v[11] = 0.45704579946446572f * y * (1.0f - 5.0f * z2);
-  v[12] = 0.3731763325901154f * z * (5.0f * z2 - 3.0f);
-  v[13] = 0.45704579946446572f * x * (1.0f - 5.0f * z2);
+  v[11] = 0.45704579946446572f * y * __fmaf_rn(-5.0f, z2, 1.0f);
+  v[12] = 0.3731763325901154f * z * __fmaf_rn(5.0f, z2, -3.0f);
+  v[13] = 0.45704579946446572f * x * __fmaf_rn(-5.0f, z2, 1.0f);
   v[14] = 1.4453057213202769f * z * (x2 - y2);
-  v[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
+  v[15] = 0.59004358992664352f * x * __fmaf_rn(3.0f, y2, -x2);
 #pragma unroll
   for (int k = 0; k < 8; ++k) out[k] = pack_h2(__float2half_rn(v[2 * k]), __float2half_rn(v[2 * k + 1]));
 }

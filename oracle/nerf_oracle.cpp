@@ -9,8 +9,18 @@
 // fixtures those produced (tests/golden/*.npz).  The MLP cannot run on the host (wmma fragments); it follows
 // the layout and wiring cited below, accumulates in fp32 and rounds to fp16 at every layer boundary.
 //
-// Build: g++ -O2 -ffp-contract=off -fopenmp -shared -fPIC  (no FMA contraction: expression trees are the
-// reference's, evaluated as written; see DESIGN.md "numerics contract").
+// Build: g++ -O2 -ffp-contract=off -fopenmp -shared -fPIC  (no IMPLICIT contraction: every fused multiply-add below
+// is an explicit fmaf; see DESIGN.md "numerics contract").
+//
+// Two numerics modes (orc_set_numerics):
+//   host (default): expression trees as the reference WRITES them, no contraction — what its kernels give when compiled
+//                   for the host; pinned bit-exactly by oracle/_ref and tests/golden/ref_tiny*.npz.
+//   cuda          : as nvcc COMPILES them for the GPU (default -fmad=true): a*b+c contracted into one fma exactly where
+//                   the reference's sm_100 SASS has an FFMA (read off `cuobjdump -sass baseline/_ref/ref_cuda_driver`:
+//                   set_rays_d, kernel_march_rays, kernel_grid, kernel_sh, linear_transformer), and the per-level grid
+//                   scale taken from the DEVICE's exp2f (MUFU.EX2; supplied by the caller, it cannot be computed here).
+//                   Pinned bit-exactly by an execution of the reference's CUDA build on a B200
+//                   (tests/golden/ref_cuda_*.npz, baseline/run_ref_cuda.py).  This is what the product follows.
 //
 // Every function cites the reference file:line it restates (paths relative to /root/reference,
 // tcnn/ = dependencies/tiny-cuda-nn/).
@@ -40,6 +50,13 @@ inline float h2f(half_t h) { return (float)h; }
 inline half_t hadd(half_t a, half_t b) { return f2h(h2f(a) + h2f(b)); }
 
 inline float clampf(float x, float lo, float hi) { return fminf(hi, fmaxf(lo, x)); }  // render_utils.h:141-144
+
+// numerics mode (see header): g_fma = contract like nvcc; g_scales = per-level grid scales as the device computes them
+bool g_fma = false;
+bool g_have_scales = false;
+float g_scales[NRF_MAX_LEVELS];
+// a*b + c: one rounding where nvcc contracts, two as written otherwise
+inline float mad(float a, float b, float c) { return g_fma ? fmaf(a, b, c) : a * b + c; }
 
 struct Levels {
   uint32_t offsets[NRF_MAX_LEVELS + 1];
@@ -74,9 +91,13 @@ int build_levels(const nrf_model_desc& d, Levels& lv, float* pls_out) {
         std::pow((float)resolution, 3) > (float)max_params ? max_params : powi_u32(resolution, 3);
     params_in_level = ((params_in_level + 7u) / 8u) * 8u;
     params_in_level = std::min(params_in_level, (1u << d.log2_hashmap_size));
-    lv.offsets[i] = offset;
+    lv.offsets[i] = offset;   // grid.h:899-931: the offset table is built on the HOST, with the host's exp2f
     lv.scales[i] = scale;
     lv.res[i] = resolution;
+    if (g_have_scales) {      // grid.h:186-187: scale and resolution are re-derived inside the kernel, on the DEVICE
+      lv.scales[i] = g_scales[i];
+      lv.res[i] = (uint32_t)(ceilf(g_scales[i])) + 1;
+    }
     offset += params_in_level;
   }
   lv.offsets[d.n_levels] = offset;
@@ -116,9 +137,10 @@ inline void ray_dir(const Frame& f, const float intr[4], int W, int p, float d[3
   float zs = 1;
   float xs = (i - intr[2]) / intr[0] * zs;
   float ys = (j - intr[3]) / intr[1] * zs;
-  float nrm = sqrtf(xs * xs + (ys * ys + zs * zs));
+  // cuda: FFMA(ys,ys,1) then FFMA(xs,xs,.); row r: FMUL(vy,R[r][1]), FFMA(vz,R[r][2],.), FFMA(vx,R[r][0],.)
+  float nrm = sqrtf(mad(xs, xs, mad(ys, ys, zs * zs)));
   float v[3] = {xs / nrm, ys / nrm, zs / nrm};
-  for (int r = 0; r < 3; ++r) d[r] = f.R[r][0] * v[0] + (f.R[r][1] * v[1] + f.R[r][2] * v[2]);
+  for (int r = 0; r < 3; ++r) d[r] = mad(f.R[r][0], v[0], mad(f.R[r][2], v[2], f.R[r][1] * v[1]));
 }
 
 // kernel_near_far_from_aabb, render_utils.h:338-392
@@ -169,9 +191,9 @@ struct Sample {
 // One loop iteration of render_utils.h:596-651.  Returns true when a sample was emitted.
 inline bool march_step(const MarchConst& m, const float* grid, const float o[3], const float d[3],
                        const float rd[3], float& t, Sample& s) {
-  const float x = clampf(o[0] + t * d[0], -m.bound, m.bound);
-  const float y = clampf(o[1] + t * d[1], -m.bound, m.bound);
-  const float z = clampf(o[2] + t * d[2], -m.bound, m.bound);
+  const float x = clampf(mad(t, d[0], o[0]), -m.bound, m.bound);   // cuda: FFMA(d, t, o)
+  const float y = clampf(mad(t, d[1], o[1]), -m.bound, m.bound);
+  const float z = clampf(mad(t, d[2], o[2]), -m.bound, m.bound);
   // mip_from_pos, render_utils.h:148-155
   const float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
   int exponent;
@@ -181,9 +203,9 @@ inline bool march_step(const MarchConst& m, const float* grid, const float o[3],
   const float mip_rbound = 1 / mip_bound;
   const uint32_t H = m.H;
   // the literal 0.5 is a double: (x*rb+1) float, then double multiply by 0.5 and H, rounded to float by clamp()
-  const int nx = clampf(0.5 * (x * mip_rbound + 1) * H, 0.0f, (float)(H - 1));
-  const int ny = clampf(0.5 * (y * mip_rbound + 1) * H, 0.0f, (float)(H - 1));
-  const int nz = clampf(0.5 * (z * mip_rbound + 1) * H, 0.0f, (float)(H - 1));
+  const int nx = clampf(0.5 * mad(x, mip_rbound, 1) * H, 0.0f, (float)(H - 1));   // cuda: FFMA(x, rb, 1), then DMUL x2
+  const int ny = clampf(0.5 * mad(y, mip_rbound, 1) * H, 0.0f, (float)(H - 1));
+  const int nz = clampf(0.5 * mad(z, mip_rbound, 1) * H, 0.0f, (float)(H - 1));
   const uint32_t cell = level * H * H * H + nx * H * H + ny * H + nz;
   if (grid[cell] > m.thresh) {
     s.x = x; s.y = y; s.z = z;
@@ -195,9 +217,10 @@ inline bool march_step(const MarchConst& m, const float* grid, const float o[3],
     s.cell = cell;
     return true;
   }
-  const float tx = (((nx + 0.5f + 0.5f * copysignf(1.0, d[0])) / (H - 1) * 2 - 1) * mip_bound - x) * rd[0];
-  const float ty = (((ny + 0.5f + 0.5f * copysignf(1.0, d[1])) / (H - 1) * 2 - 1) * mip_bound - y) * rd[1];
-  const float tz = (((nz + 0.5f + 0.5f * copysignf(1.0, d[2])) / (H - 1) * 2 - 1) * mip_bound - z) * rd[2];
+  // cuda: FADD(n,.5), FFMA(sign,.5,.) [exact], IEEE div, FFMA(q,2,-1) [exact], FFMA(.,mip_bound,-x), FMUL(.,rd)
+  const float tx = mad(mad((nx + 0.5f + 0.5f * copysignf(1.0, d[0])) / (H - 1), 2, -1), mip_bound, -x) * rd[0];
+  const float ty = mad(mad((ny + 0.5f + 0.5f * copysignf(1.0, d[1])) / (H - 1), 2, -1), mip_bound, -y) * rd[1];
+  const float tz = mad(mad((nz + 0.5f + 0.5f * copysignf(1.0, d[2])) / (H - 1), 2, -1), mip_bound, -z) * rd[2];
   const float tt = t + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
   do {
     const float dt = clampf(t * m.dt_gamma, m.dt_min, m.dt_max);
@@ -228,7 +251,7 @@ void encode_sample(const Levels& lv, uint32_t L, const uint16_t* table, const fl
     float w[3];
     uint32_t g[3];
     for (int dim = 0; dim < 3; ++dim) {  // pos_fract, identity interpolation
-      float p = u[dim] * scale + 0.5f;
+      float p = mad(u[dim], scale, 0.5f);   // cuda: FFMA(input, scale, .5)
       int tmp = floorf(p);
       g[dim] = (uint32_t)tmp;
       w[dim] = p - (float)tmp;
@@ -256,6 +279,26 @@ void sh4(const float in[3], uint16_t out[16]) {
   float x = in[0] * 2.f - 1.f, y = in[1] * 2.f - 1.f, z = in[2] * 2.f - 1.f;
   float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
   float v[16];
+  if (g_fma) {   // the contractions of kernel_sh<__half>'s SASS: entries 6, 8, 9, 11, 12, 13, 15
+    v[0] = 0.28209479177387814f;
+    v[1] = -0.48860251190291987f * y;
+    v[2] = 0.48860251190291987f * z;
+    v[3] = -0.48860251190291987f * x;
+    v[4] = 1.0925484305920792f * xy;
+    v[5] = -1.0925484305920792f * yz;
+    v[6] = fmaf(0.94617469575755997f, z2, -0.31539156525251999f);
+    v[7] = -1.0925484305920792f * xz;
+    v[8] = fmaf(0.54627421529603959f, x2, -(0.54627421529603959f * y2));
+    v[9] = 0.59004358992664352f * y * fmaf(-3.0f, x2, y2);
+    v[10] = 2.8906114426405538f * xy * z;
+    v[11] = 0.45704579946446572f * y * fmaf(-5.0f, z2, 1.0f);
+    v[12] = 0.3731763325901154f * z * fmaf(5.0f, z2, -3.0f);
+    v[13] = 0.45704579946446572f * x * fmaf(-5.0f, z2, 1.0f);
+    v[14] = 1.4453057213202769f * z * (x2 - y2);
+    v[15] = 0.59004358992664352f * x * fmaf(3.0f, y2, -x2);
+    for (int k = 0; k < 16; ++k) out[k] = h2bits(f2h(v[k]));
+    return;
+  }
   v[0] = 0.28209479177387814f;
   v[1] = -0.48860251190291987f * y;
   v[2] = 0.48860251190291987f * z;
@@ -535,7 +578,8 @@ long long orc_render_frame(const nrf_model_desc* desc, const uint16_t* mlp_weigh
     while (t < far && c < NRF_MAX_STEPS) {
       if (!march_step(m, grid, f.o, d, rd, t, s)) continue;
       ++c;
-      const float u[3] = {pos_w * s.x + 0.5f, pos_w * s.y + 0.5f, pos_w * s.z + 0.5f};
+      // linear_transformer (common_device.cuh:31-36): weight*input + bias — cuda: one FFMA
+      const float u[3] = {mad(pos_w, s.x, 0.5f), mad(pos_w, s.y, 0.5f), mad(pos_w, s.z, 0.5f)};
       uint16_t enc[32];
       float o4[4];
       encode_sample(lv, 16, table, u, enc, nullptr);
@@ -714,6 +758,15 @@ void orc_tonemap(int n, const float* accum, float exposure, const float backgrou
     if (clamp_output) for (int k = 0; k < 4; ++k) c[k] = fminf(fmaxf(c[k], 0.0f), 1.0f);
     std::memcpy(out + (size_t)i * 4, c, 16);
   }
+}
+
+// Numerics mode of every later call (see header): fma != 0 -> "cuda", else "host"; scales (may be NULL) = the n per-level
+// grid scales as the DEVICE's exp2f gives them (from the product, or from tests/golden/ref_cuda_*.npz).
+int orc_set_numerics(int fma, const float* scales, int n) {
+  g_fma = fma != 0;
+  g_have_scales = scales != nullptr && n > 0 && n <= NRF_MAX_LEVELS;
+  if (g_have_scales) for (int i = 0; i < n; ++i) g_scales[i] = scales[i];
+  return 0;
 }
 
 int orc_num_threads(void) {

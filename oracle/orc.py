@@ -46,10 +46,18 @@ def _p(a, ty):
 
 
 class Oracle:
-    """Holds a model (fp16 weights + table, float grid) and exposes each stage of the hot path."""
+    """Holds a model (fp16 weights + table, float grid) and exposes each stage of the hot path.
 
-    def __init__(self, desc, params_f32, grid, aabb):
+    numerics: "host" = the reference's expression trees as written (what its kernels give compiled for the host; pinned by
+    oracle/_ref); "cuda" = as nvcc compiles them for the GPU — a*b+c contracted where the reference's sm_100 SASS has an
+    FFMA — with `scales` = the per-level grid scales as the device's exp2f gives them (NerfRender.level_scales(), or the
+    `level_scales` array of tests/golden/ref_cuda_*.npz); pinned by an execution of the reference's CUDA build."""
+
+    def __init__(self, desc, params_f32, grid, aabb, numerics="host", scales=None):
         self.l = lib()
+        assert numerics in ("host", "cuda")
+        self.fma = numerics == "cuda"
+        self.scales = None if scales is None else np.ascontiguousarray(scales, np.float32)
         self.desc = desc
         self.grid = np.ascontiguousarray(grid, np.float32)
         self.aabb = np.ascontiguousarray(aabb, np.float32)
@@ -59,7 +67,12 @@ class Oracle:
         self.mlp = np.ascontiguousarray(p16[:10240])
         self.table = np.ascontiguousarray(p16[10240:])
 
+    def _mode(self):
+        n = 0 if self.scales is None else int(self.scales.size)
+        self.l.orc_set_numerics(int(self.fma), _p(self.scales, C.c_float), n)
+
     def level_table(self):
+        self._mode()
         L = self.desc.n_levels
         offs, sc, res = np.zeros(L + 1, np.uint32), np.zeros(L, np.float32), np.zeros(L, np.uint32)
         pls = C.c_float()
@@ -69,6 +82,7 @@ class Oracle:
         return offs, sc, res, pls.value
 
     def rays(self, intr, pose, W, H, pix0=0, n=None):
+        self._mode()
         n = W * H - pix0 if n is None else n
         o, d = np.zeros(3, np.float32), np.zeros((n, 3), np.float32)
         nr, fr = np.zeros(n, np.float32), np.zeros(n, np.float32)
@@ -77,6 +91,7 @@ class Oracle:
         return o, d, nr, fr
 
     def march(self, o, d, nears, fars, want_samples=True):
+        self._mode()
         n = d.shape[0]
         counts = np.zeros(n, np.int32)
         args = (C.byref(self.desc), _p(self.grid, C.c_float), n, _p(o, C.c_float), _p(d, C.c_float),
@@ -90,6 +105,7 @@ class Oracle:
         return counts, samples[:total]
 
     def encode(self, positions, want_indices=False):
+        self._mode()
         n = positions.shape[0]
         enc = np.zeros((n, 32), np.uint16)
         idx = np.zeros((n, self.desc.n_levels, 8), np.uint32) if want_indices else None
@@ -100,12 +116,14 @@ class Oracle:
         return (enc, idx) if want_indices else enc
 
     def sh(self, dirs01):
+        self._mode()
         n = dirs01.shape[0]
         out = np.zeros((n, 16), np.uint16)
         self.l.orc_sh(n, _p(np.ascontiguousarray(dirs01, np.float32), C.c_float), _p(out, C.c_uint16))
         return out
 
     def network(self, enc_u16, dirs01):
+        self._mode()
         n = enc_u16.shape[0]
         out = np.zeros((n, 4), np.float32)
         rc = self.l.orc_network(C.byref(self.desc), _p(self.mlp, C.c_uint16), n,
@@ -115,6 +133,7 @@ class Oracle:
         return out
 
     def samples(self, positions01, dirs01):
+        self._mode()
         n = positions01.shape[0]
         out = np.zeros((n, 4), np.float32)
         rc = self.l.orc_samples(C.byref(self.desc), _p(self.mlp, C.c_uint16), _p(self.table, C.c_uint16), n,
@@ -125,6 +144,7 @@ class Oracle:
 
     def density_grid(self, decay=0.95, reset=True, seed=0, jitter=False, grid=None):
         """generate_density_grid restatement: returns (new float grid [C*H^3], mean density)."""
+        self._mode()
         g = np.ascontiguousarray(self.grid if grid is None else grid, np.float32).copy()
         self.l.orc_density_grid.restype = C.c_float
         mean = self.l.orc_density_grid(C.byref(self.desc), _p(self.mlp, C.c_uint16), _p(self.table, C.c_uint16),
@@ -134,6 +154,7 @@ class Oracle:
         return g, float(mean)
 
     def render(self, intr, pose, W, H, pix0=0, npix=None):
+        self._mode()
         npix = W * H - pix0 if npix is None else npix
         rgb, depth = np.zeros((npix, 3), np.float32), np.zeros(npix, np.float32)
         counts = np.zeros(npix, np.int32)
@@ -156,6 +177,13 @@ class Oracle:
     def set_num_threads(self, n):
         """OpenMP threads of every later call (overrides an inherited OMP_NUM_THREADS); returns the count in effect."""
         return self.l.orc_set_num_threads(int(n))
+
+
+def cuda_oracle(renderer, desc, params_f32, grid, aabb):
+    """Oracle in the reference-CUDA numerics for comparison with a renderer: the per-level grid scales are the ones the
+    renderer's device evaluated (the same MUFU.EX2 the reference's kernel_grid uses); `renderer` must hold a model with
+    the same encoding parameters."""
+    return Oracle(desc, params_f32, grid, aabb, numerics="cuda", scales=renderer.level_scales())
 
 
 def half_to_float(u16):

@@ -25,7 +25,7 @@ def pair(request, built_lib):
     sc = syn.make_scene(request.param)
     r = NerfRender(1)
     r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
-    O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
+    O = orc.cuda_oracle(r, sc.desc, sc.params, sc.grid, sc.aabb)
     yield request.param, sc, r, O
     r.close()
 
@@ -39,10 +39,15 @@ def rel_err(a, b):
 
 def test_level_table_matches_oracle(pair):
     from nerf_cuda_b200 import level_table
-    _, sc, _, O = pair
+    _, sc, r, O = pair
+    # host table (offsets from the host exp2f, grid.h:602-627) against the oracle in host numerics
     offs, scl, res = level_table(sc.desc)
-    o2, s2, r2, _ = O.level_table()
+    o2, s2, r2, _ = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb).level_table()
     assert np.array_equal(offs, o2) and np.array_equal(bits(scl), bits(s2)) and np.array_equal(res, r2)
+    # the scales the kernels use come from the device's exp2f (as in kernel_grid); the oracle built from them keeps the
+    # host offsets and reports the device scales
+    o3, s3, _, _ = O.level_table()
+    assert np.array_equal(offs, o3) and np.array_equal(bits(r.level_scales()), bits(s3))
 
 
 @pytest.mark.parametrize("az", [0.0, 77.0, 201.0])
@@ -167,7 +172,7 @@ def test_frame_sigmoid_activation(built_lib):
     sc = syn.make_scene("tiny", rgb_activation=syn.NRF_ACT_SIGMOID)
     r = NerfRender(1)
     r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
-    O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
+    O = orc.cuda_oracle(r, sc.desc, sc.params, sc.grid, sc.aabb)
     W, H = 64, 48
     intr, pose = syn.intrinsics(W, H), syn.look_at_pose(4.0, 20.0, 10.0)
     r.set_resolution((W, H))
@@ -262,7 +267,7 @@ def test_density_grid_regeneration(built_lib, bound, cascades):
     n = sc.grid.size
     r = NerfRender(1)
     r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
-    O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
+    O = orc.cuda_oracle(r, sc.desc, sc.params, sc.grid, sc.aabb)
     g0, b0 = r.density_grid(n)
     assert np.array_equal(g0, sc.grid)
     assert np.array_equal(np.unpackbits(b0.view(np.uint8), bitorder="little").astype(bool), sc.grid > 0.01)
@@ -287,7 +292,7 @@ def test_density_grid_regeneration(built_lib, bound, cascades):
     g, _ = r.density_grid(n)
     d2 = syn.ModelDesc.from_buffer_copy(sc.desc)
     d2.mean_density = mean
-    O2 = orc.Oracle(d2, sc.params, g, sc.aabb)
+    O2 = orc.cuda_oracle(r, d2, sc.params, g, sc.aabb)
     W = H = 48
     intr, pose = syn.intrinsics(W, H), syn.look_at_pose(12.0 if cascades > 1 else 4.0, 20.0, 60.0)
     o, dirs, nears, fars = O2.rays(intr, pose, W, H)
@@ -482,7 +487,7 @@ def test_sample_t_cache_replay_and_resume(pair, monkeypatch):
     a, b = frames
     assert a[4] == b[4] and a[4] > 64 * W * H // 4
     assert all(np.array_equal(x, y) for x, y in zip(a[:4], b[:4]))
-    O2 = orc.Oracle(sc.desc, sc.params, grid, sc.aabb)
+    O2 = orc.cuda_oracle(r, sc.desc, sc.params, grid, sc.aabb)
     rgb2, dep2, cnt2 = O2.render(intr, pose, W, H)
     assert np.array_equal(a[3], cnt2) and np.abs(a[1] - rgb2).max() <= IMG_TOL
 
@@ -546,7 +551,7 @@ def test_full_size_c3_frame(built_lib, pi):
     rgb, dep, cnt = (x.copy() for x in r.float_frame())
     n_whole = r.stats().n_samples
     assert u8.shape == (H, W, 3) and cnt.min() >= 0 and cnt.max() <= 1024 and n_whole >= int(cnt.sum()) > 0
-    O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
+    O = orc.cuda_oracle(r, sc.desc, sc.params, sc.grid, sc.aabb)
     for row in (3, H // 2 - 1, H - 5):
         pix0, npix = row * W, 2 * W
         rgb2, dep2, cnt2 = O.render(intr, poses[pi], W, H, pix0, npix)

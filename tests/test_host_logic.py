@@ -176,7 +176,7 @@ def test_snapshot_reader_errors_match_reference(built_lib, tmp_path):
     import msgpack
     # wrong extension / missing file: nerf_render.cu:73-76,98,105-107
     with pytest.raises(NerfError) as e:
-        _inspect(str(tmp_path / "model.json"))
+        _inspect(str(tmp_path / "model.bin"))
     assert e.value.code == -4 and ".msgpack" in str(e.value)
     with pytest.raises(NerfError) as e:
         _inspect(str(tmp_path / "missing.msgpack"))
