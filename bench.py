@@ -46,16 +46,11 @@ def peaks():
     return dict(hbm=6650.0, tf=1590.0, tf_sus=1400.0, src="fallback")
 
 
-def ncu_traffic(samples_per_launch):
-    """DRAM traffic of the dominant kernel per launch, from the committed ncu --set full capture of one full-size launch
-    (profiles/traffic_k_network.json, written by scripts/ncu_traffic.py): bytes per sample x this run's samples per launch."""
+def ncu_capture():
+    """Figures of the committed ncu --set full capture of one full-size k_network launch (profiles/traffic_k_network.json,
+    written by scripts/ncu_traffic.py): DRAM bytes per sample, L1 wavefront pipe and tensor pipe utilisation."""
     p = os.path.join(ROOT, "profiles", "traffic_k_network.json")
-    if not os.path.exists(p):
-        return {"traffic": None}
-    d = json.load(open(p))
-    return {"traffic": d["dram_bytes_per_sample"] * samples_per_launch,
-            "traffic_source": f"{d['dram_bytes_per_sample']:.1f} B/sample ({d['source']}, {d['workload']}) x samples per launch; "
-                              f"L1 wavefront pipe {d['l1_wavefronts_pct_of_peak']:.0f} % of peak, tensor pipe {d['tensor_pipe_pct']:.1f} % in that capture"}
+    return json.load(open(p)) if os.path.exists(p) else None
 
 
 class ClockSampler:
@@ -113,6 +108,7 @@ def cpu_arm(workload, steps, warmup, target_s=4.0):
     cfg, W, H, _ = WORKLOADS[workload]
     sc = syn.make_scene(cfg)
     O = orc.Oracle(sc.desc, sc.params, sc.grid, sc.aabb)
+    O.set_num_threads(os.cpu_count() or 1)     # torchrun exports OMP_NUM_THREADS=1 to its workers: use every host core anyway
     intr, poses = syn.intrinsics(W, H), poses_for(workload)
     mid = (H // 2) * W
     t0 = time.perf_counter()
@@ -133,6 +129,41 @@ def cpu_arm(workload, steps, warmup, target_s=4.0):
                 sample=f"{rows} full pixel rows ({npix} rays) centred in the {W}x{H} frame per step, "
                        f"{samples / max(len(times), 1) / npix:.1f} samples/ray",
                 samples_per_s=samples / tot)
+
+
+def ref_cuda_arm(workload, steps, warmup, exe="ref_cuda_driver_d1"):
+    """Times the reference's OWN CUDA renderer (baseline/_ref/<exe>: src/nerf_render.cu + tiny-cuda-nn compiled for sm_100
+    by baseline/build_ref_cuda.sh) on this box's GPU 0 through its public call NerfRender::render_frame — host pose in,
+    host u8 frame out, wall clock around the calls as src/main.cu:159-164 times it.  The model reaches it the way a trained
+    export does: as a .msgpack snapshot through reload_network_from_file.  Returns None when the binary or a GPU is absent."""
+    import tempfile
+    from nerf_cuda_b200 import synthetic as syn
+    from nerf_cuda_b200.snapshot import write_snapshot
+    path = os.path.join(ROOT, "baseline", "_ref", exe)
+    if not os.path.exists(path):
+        return None
+    try:
+        if subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True).stdout.count("GPU ") < 1:
+            return None
+    except OSError:
+        return None
+    cfg, W, H, _ = WORKLOADS[workload]
+    sc = syn.make_scene(cfg)
+    poses = np.stack(poses_for(workload)).astype(np.float32)
+    with tempfile.TemporaryDirectory() as tmp:
+        snap, pp = os.path.join(tmp, "model.msgpack"), os.path.join(tmp, "poses.bin")
+        write_snapshot(snap, sc.desc, sc.params, sc.grid, sc.aabb)
+        poses.tofile(pp)
+        cam = [repr(float(x)) for x in syn.intrinsics(W, H)]
+        env = dict(os.environ, CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "0").split(",")[0])
+        r = subprocess.run([path, snap, tmp, "bench", str(W), str(H), *cam, pp, str(len(poses)), str(warmup), str(steps)],
+                           capture_output=True, text=True, env=env, timeout=1500)
+    if r.returncode != 0:
+        return {"error": f"{exe} exited {r.returncode}: {r.stderr[-300:]}"}
+    ev = [json.loads(ln) for ln in r.stdout.splitlines() if ln.startswith("{")]
+    b = [e for e in ev if e.get("event") == "bench"][0]
+    return dict(value=W * H / (b["ms_per_step"] * 1e-3), ms_per_step=b["ms_per_step"], exe=exe,
+                load_s=[e for e in ev if e.get("event") == "loaded"][0]["seconds"])
 
 
 # --------------------------------------------------------------------------------------------- GPU arm
@@ -157,18 +188,19 @@ def gpu_arm(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     cfg, W, H, _ = WORKLOADS[args.workload]
-    sc = syn.make_scene(cfg)
+    sc = syn.make_scene(cfg, opaque=args.scene == "opaque")
     intr, poses = syn.intrinsics(W, H), poses_for(args.workload)
     r = NerfRender(1, device_ids=[local])
     r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
-    if world > 1:
+    pose_par = world > 1 and args.shard == "poses"   # whole frames per rank (pose k -> rank k % world), no intra-frame traffic
+    if world > 1 and not pose_par:
         r.set_shard(rank, world)
     r.set_resolution((W, H))
     n_local = r.local_rays()
     ext = torch.cuda.ExternalStream(r.stream(), device=torch.device("cuda", local))
     rgb_ptr, dep_ptr, _ = r.device_outputs()
-    gatherer = local_rgb = host_frame = fence = None
-    peer = world > 1 and args.gather == "peer"
+    gatherer = local_rgb = host_frame = None
+    peer = world > 1 and args.gather == "peer" and not pose_par
     if peer:
         # the gather is fused into the composite kernel: rank 0 exports its frame buffer (CUDA IPC), every other rank
         # maps it and stores its pixels there over NVLink; the only collective left is a 4-byte completion fence
@@ -178,10 +210,10 @@ def gpu_arm(args):
         dist.broadcast(handle, 0)
         if rank != 0:
             r.peer_frame_attach(bytes(handle.cpu().numpy().tobytes()))
-        with torch.cuda.stream(ext):
-            fence = torch.zeros(1, dtype=torch.int32, device="cuda")
+        if rank == 0:
+            r.peer_frame_copy_out(True)   # every frame is copied to a pinned host slot behind its fence, on the copy stream
         dist.barrier()
-    elif world > 1:
+    elif world > 1 and not pose_par:
         from nerf_cuda_b200.multigpu import FrameGather, FrameSharding
         sh = FrameSharding(W, H, world)
         with torch.cuda.stream(ext):
@@ -191,19 +223,21 @@ def gpu_arm(args):
 
     def frame(i, to_host):
         """One step.  to_host: reference-facing semantics (host pose in, host u8 frame out on rank 0)."""
-        pose = poses[i % len(poses)]
+        pose = poses[(i * world + rank) % len(poses)] if pose_par else poses[i % len(poses)]
         with torch.cuda.stream(ext):
-            if world == 1:
+            if world == 1 or pose_par:
                 if to_host:
                     return r.render_frame(intr, pose)
                 r.render_frame_device(intr, pose)
                 return None
             r.render_frame_device(intr, pose)
             if peer:
-                dist.all_reduce(fence)                      # completion fence (stream-ordered): every rank's stores landed
-                if to_host and rank == 0:                   # the peer frame is double-buffered: the next frame's stores go
-                    r.peer_frame_to_host()                  # to the other half, and ITS fence orders this copy before the
-                    ext.synchronize()                       # half is written again — one collective per frame
+                # nothing else on the device side: the pixel stores ARE the gather and the fence is one-sided (each rank's
+                # stream publishes its frame number after its composite; rank 0's copy stream waits for all of them).
+                # Reference-facing: the frame's D2H runs behind its fence while the next frame renders; the step hands
+                # over the PREVIOUS frame (two pinned slots), the last one is drained inside the timed region.
+                if to_host:
+                    return r.peer_frame_collect(1)
                 return None
             full = gatherer(local_rgb)                      # NCCL gather of packed u8 tiles + tile transpose on rank 0
             if to_host and rank == 0:
@@ -211,7 +245,14 @@ def gpu_arm(args):
                 ext.synchronize()
         return None
 
-    def timed(to_host, steps, warmup, collect_stats=False):
+    def drain(to_host):
+        """End of a timed loop, inside the timed region: everything the last frame still has in flight."""
+        if peer:
+            if to_host:
+                r.peer_frame_collect(0)
+            r.frame_join()
+
+    def timed(to_host, steps, warmup):
         for i in range(warmup):
             frame(i, to_host)
         r.synchronize()
@@ -219,13 +260,10 @@ def gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        net_ms, samples = [], []
         e0.record(ext)
         for i in range(steps):
             frame(warmup + i, to_host)
-            if collect_stats:
-                st = r.stats()
-                net_ms.append(st.ms_network); samples.append(int(st.n_samples))
+        drain(to_host)
         e1.record(ext)
         e1.synchronize()
         torch.cuda.synchronize()
@@ -234,7 +272,21 @@ def gpu_arm(args):
             t = torch.tensor([ms], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
-        return ms, net_ms, samples
+        return ms
+
+    def frame_stats(steps, warmup):
+        """Untimed pass over the frames of the timed loop, one host sync per frame, for the per-frame counters and the
+        per-stage event times (reading them inside the timed loop would serialise it)."""
+        keys = ("ms_setup", "ms_march", "ms_network", "ms_composite", "ms_total", "n_samples", "n_samples_marched", "n_samples_used", "n_rounds")
+        acc = {k: [] for k in keys}
+        for i in range(steps):
+            frame(warmup + i, False)
+            st = r.stats()
+            for k in keys:
+                acc[k].append(float(getattr(st, k)))
+        drain(False)
+        r.synchronize()
+        return acc
 
     sampler = ClockSampler(local)
     if rank == 0:
@@ -243,8 +295,17 @@ def gpu_arm(args):
         frame(i, False)
     r.synchronize()                      # sync point: the buffers grow to the largest frame enqueued so far
     ovf0 = r.overflowed_frames()
-    ms_dev, _, _ = timed(False, args.steps, args.warmup)
-    ms_e2e, net_ms, samples = timed(True, args.steps, max(3, args.warmup // 2), collect_stats=True)
+    ms_dev = timed(False, args.steps, args.warmup)
+    ms_e2e = timed(True, args.steps, max(3, args.warmup // 2))
+    fs = frame_stats(args.steps, args.warmup)
+    net_ms, samples, marched, used, rounds = fs["ms_network"], fs["n_samples"], fs["n_samples_marched"], fs["n_samples_used"], fs["n_rounds"]
+    per_rank = {k: float(np.mean(v)) for k, v in fs.items()}
+    if world > 1:   # every rank's counters and stage times on the JSON line (load balance of the tile sharding)
+        allr = [None] * world
+        dist.all_gather_object(allr, per_rank)
+        per_rank = allr
+    else:
+        per_rank = [per_rank]
     # frames are enqueued without host syncs: one that did not fit the sample buffers would have been rendered
     # incompletely (and too fast) — none may have occurred inside the timed regions
     ovf = r.overflowed_frames() - ovf0
@@ -270,47 +331,79 @@ def gpu_arm(args):
         smp_total = float(t.item())
     else:
         smp_total = float(np.mean(samples))
-    rays = W * H
+    rays = W * H * (world if pose_par else 1)   # per step: one frame, or one frame per rank when poses are sharded
     pk = peaks()
-    table_mb = 2 * int(syn.level_table(sc.desc)[0][-1]) * 2 / 1e6
+    table_bytes = 2 * int(syn.level_table(sc.desc)[0][-1]) * 2
+    table_mb = table_bytes / 1e6
+    l2_resident = table_mb < 100
+    # roofline denominators measured NOW on this GPU (kernels_probe.cu): L2->SM streaming bandwidth over a window the size
+    # of the table (every CTA streams the whole window, so no SM's L1 can hold it) or HBM streaming when the table does not
+    # fit L2; and the random-sector gather rate over the same window (the access shape of a hashed level)
+    mem = {}
+    if rank == 0:
+        win = max(8 << 20, (table_bytes + (1 << 20) - 1) >> 20 << 20)
+        mem["stream_gbs"] = r.bench_memory(2 if l2_resident else 0, win if l2_resident else 4 << 30, 3)[0]
+        mem["gather_gloads"] = r.bench_memory(1, win, 3)[1]
     out = None
     if rank == 0:
         net = float(np.mean(net_ms))
         s_k = float(np.mean(samples))  # rank 0's samples per launch
-        alg_bytes = s_k * (GATHER_BYTES_PER_SAMPLE + STREAM_BYTES_PER_SAMPLE)
+        n_launch = float(np.mean(rounds))   # k_network launches per frame (one per evaluation round); s_k, net are per frame
+        alg_bytes = s_k * GATHER_BYTES_PER_SAMPLE
         achieved = alg_bytes / (net * 1e-3) / 1e9
+        ncu = ncu_capture()
         out = {
             "metric": "rays_per_second_1080p" if args.workload == "C3" else f"rays_per_second_{args.workload}",
             "value": rays * args.steps / (ms_dev * 1e-3), "unit": "rays/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong",
+            "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak" if pose_par else "strong",
             "vs_baseline": None, "dtype": "f16", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {W}x{H} frame, bound {sc.desc.bound:g}, {sc.desc.cascades} cascades, "
                                    f"log2_hashmap_size {sc.desc.log2_hashmap_size}, base.json MLPs, random-init weights, "
                                    f"synthetic occupancy, {len(poses)} orbit poses cycled",
-                       "sharding": "whole frame" if world == 1 else (
+                       "sharding": "whole frame" if world == 1 else (f"pose-parallel: every step renders {world} frames, pose k on rank k % {world}, whole frames, "
+                                                                     f"each rank returns its own frame to its host; no intra-frame traffic" if pose_par else
                            f"32x32-pixel tiles round-robin over {world} ranks; every rank's composite kernel stores its u8 pixels straight into "
-                           f"rank 0's frame over NVLink (CUDA IPC peer stores), 4-byte NCCL all-reduce as completion fence" if peer else
+                           f"rank 0's frame over NVLink (CUDA IPC peer stores); completion fence one-sided: per-rank st.release.sys sequence "
+                           f"flags polled by a one-warp kernel on rank 0's copy stream, no collective; rank 0's D2H double-buffered behind the fence" if peer else
                            f"32x32-pixel tiles round-robin over {world} ranks, NCCL gather of packed u8 tiles to rank 0"),
-                       "samples_per_frame": smp_total, "samples_per_ray": smp_total / rays,
+                       "scene": args.scene, "samples_per_frame": smp_total, "samples_per_ray": smp_total / rays,
+                       "samples_rank0": {"marched": float(np.mean(marched)), "evaluated": s_k, "composited": float(np.mean(used)),
+                                         "evaluation_rounds": n_launch},
                        "l2": f"inputs larger than L2: each frame streams {smp_total / world * 56 / 1e6:.0f} MB of sample records per GPU (20 B written by the march, 16 read + 8 written by the network, 12 read by the composite) "
                              f"and the pose changes every step; the {table_mb:.1f} MB hash table is "
                              + ("L2-resident by design" if table_mb < 100 else "far larger than the 126 MB L2 (HBM-resident gather)")},
             "e2e": {"value": rays * args.steps / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
                     "batch_call_value": batch_rps, "h2d_bytes_per_step": 80, "d2h_bytes_per_step": rays * 4 + 8 if (world == 1 or peer) else rays * 3 + 8},
-            "gpu_launches": 5 * args.steps,
+            "per_rank": [{"rank": k, "samples_evaluated": p["n_samples"], "samples_marched": p["n_samples_marched"],
+                          "stage_ms": {"rays+count+scan": p["ms_setup"], "emit": p["ms_march"], "network": p["ms_network"],
+                                       "composite": p["ms_composite"], "total": p["ms_total"]}} for k, p in enumerate(per_rank)],
+            "gpu_launches": 5 * int(sum(rounds)) + (int(3 * args.steps) if peer else 0),   # rank 0, timed device loop; per frame and round: count (or round sums), scan, emit, network, composite (+ 3 one-warp fence kernels per frame with the peer frame)
             "overflowed_timed_frames": int(ovf),
             "clocks": clocks,
-            "roofline": {"kernel": "k_network<2> (hash-grid gather + tcgen05 MLP, fused)", "bound": "hbm",
-                         "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s", "frac": achieved / pk["hbm"],
-                         **(ncu_traffic(s_k) if table_mb < 100 else {"traffic": None}), "peak_source": pk["src"] + (" (HBM copy; the table is L2-resident, so >1 is possible)" if table_mb < 100 else " (HBM copy)"),
-                         "algorithmic_bytes_per_sample": GATHER_BYTES_PER_SAMPLE + STREAM_BYTES_PER_SAMPLE,
-                         "samples_per_launch": s_k, "ms_per_launch": net,
+            "roofline": {"kernel": "k_network<2> (hash-grid gather + tcgen05 MLP, fused)",
+                         "bound": "l2" if l2_resident else "hbm",
+                         "achieved": achieved, "peak": mem["stream_gbs"], "unit": "GB/s", "frac": achieved / mem["stream_gbs"],
+                         "peak_source": (f"L2->SM streaming read bandwidth over a {table_mb:.0f} MB window, measured live on this GPU "
+                                         "(nrf_bench_memory mode 2); the table is L2-resident, so HBM is not the bound" if l2_resident else
+                                         "HBM streaming read bandwidth over a 4 GB window, measured live on this GPU (nrf_bench_memory mode 0)"),
+                         "hbm_copy_peak": pk["hbm"], "hbm_copy_peak_source": pk["src"], "frac_of_hbm_copy_peak": achieved / pk["hbm"],
+                         "algorithmic_bytes_per_sample": GATHER_BYTES_PER_SAMPLE,
+                         "stream_bytes_per_sample_not_counted": STREAM_BYTES_PER_SAMPLE,
+                         "samples_per_launch": s_k / n_launch, "ms_per_launch": net / n_launch, "launches_per_frame": n_launch,
+                         "traffic": (ncu["dram_bytes_per_sample"] * s_k / n_launch) if ncu and l2_resident else None,
+                         "traffic_source": (f"{ncu['dram_bytes_per_sample']:.1f} DRAM B/sample ({ncu['source']}, {ncu['workload']}) x samples per launch"
+                                            if ncu and l2_resident else None),
+                         # the pipes that actually limit the kernel (ncu --set full of one full-size launch, profiles/)
+                         "l1_wavefront_frac": ncu["l1_wavefronts_pct_of_peak"] / 100 if ncu else None,
+                         "tensor_pipe_pct": ncu["tensor_pipe_pct"] if ncu else None,
+                         "gather_lookups_per_ns": s_k * 128 / (net * 1e-3) / 1e9,
+                         "random_sector_gather_loads_per_ns_measured": mem["gather_gloads"],
                          "mlp_tflops_in_fused": s_k * MLP_FLOP_PER_SAMPLE / (net * 1e-3) / 1e12,
                          "mlp_frac_of_sustained_bf16_peak": s_k * MLP_FLOP_PER_SAMPLE / (net * 1e-3) / 1e12 / pk["tf_sus"]},
             "stages_alone": {
                 **stage,
                 "encode_gather_gbs": smp_local * GATHER_BYTES_PER_SAMPLE / (stage["encode_ms"] * 1e-3) / 1e9,
-                "encode_frac_of_hbm_peak": smp_local * GATHER_BYTES_PER_SAMPLE / (stage["encode_ms"] * 1e-3) / 1e9 / pk["hbm"],
+                "encode_frac_of_measured_stream_peak": smp_local * GATHER_BYTES_PER_SAMPLE / (stage["encode_ms"] * 1e-3) / 1e9 / mem["stream_gbs"],
                 "mlp_tflops": smp_local * MLP_FLOP_PER_SAMPLE / (stage["mlp_ms"] * 1e-3) / 1e12,
                 "mlp_frac_of_burst_bf16_peak": smp_local * MLP_FLOP_PER_SAMPLE / (stage["mlp_ms"] * 1e-3) / 1e12 / pk["tf"],
             },
@@ -327,7 +420,7 @@ def gpu_arm(args):
         print(json.dumps(out), flush=True)
     # teardown order matters: every torch tensor that was used on the library's stream must be released (and the
     # caching allocator's blocks for that stream returned) BEFORE nrf_destroy destroys the stream
-    gatherer = local_rgb = host_frame = frame = timed = fence = None
+    gatherer = local_rgb = host_frame = frame = timed = drain = None
     if peer:
         torch.cuda.synchronize()
         dist.barrier()
@@ -344,6 +437,123 @@ def gpu_arm(args):
     r.close()
 
 
+def inproc_arm(args):
+    """--mode inproc: ONE process drives all N GPUs through nrf_create(n_gpus) — the path ngp::NerfRender(n) and
+    `render_server --gpus n` use (the reference's own multi-GPU shape: one process, NGPU devices, common.h:91).  Tiles are
+    sharded round-robin over the devices, every device's composite stores its pixels into device 0's frame over NVLink,
+    device 0's stream waits on the other devices' events; no collective, no second process."""
+    import torch
+    from nerf_cuda_b200 import NerfRender, synthetic as syn
+    n = args.gpus
+    cfg, W, H, _ = WORKLOADS[args.workload]
+    sc = syn.make_scene(cfg, opaque=args.scene == "opaque")
+    intr, poses = syn.intrinsics(W, H), poses_for(args.workload)
+    torch.cuda.set_device(0)
+    r = NerfRender(n)
+    r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    r.set_resolution((W, H))
+    ext = torch.cuda.ExternalStream(r.stream(), device=torch.device("cuda", 0))
+    sampler = ClockSampler(0)
+    sampler.start()
+    for i in range(len(poses)):
+        r.render_frame_device(intr, poses[i])
+    r.synchronize()
+    ovf0 = r.overflowed_frames()
+
+    def timed(to_host, steps, warmup):
+        for i in range(warmup):
+            (r.render_frame if to_host else r.render_frame_device)(intr, poses[i % len(poses)])
+        r.synchronize()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(ext)
+        for i in range(steps):
+            (r.render_frame if to_host else r.render_frame_device)(intr, poses[(warmup + i) % len(poses)])
+        r.frame_join()                     # device 0's stream waits for the other devices' last kernels
+        e1.record(ext)
+        e1.synchronize()
+        for d in range(n):
+            torch.cuda.synchronize(d)
+        return e0.elapsed_time(e1)
+
+    ms_dev = timed(False, args.steps, args.warmup)
+    ms_e2e = timed(True, args.steps, max(3, args.warmup // 2))
+    ovf = r.overflowed_frames() - ovf0
+    if ovf:
+        raise RuntimeError(f"{ovf} timed frame(s) overflowed the sample buffers: the measurement is invalid")
+    pb = np.stack([poses[(args.warmup + i) % len(poses)] for i in range(args.steps)])
+    r.render_batch(intr, pb[: min(len(pb), len(poses))])
+    tb = time.perf_counter()
+    r.render_batch(intr, pb)
+    batch_rps = W * H * len(pb) / (time.perf_counter() - tb)
+    clocks = sampler.stop()
+    rounds = []
+    for i in range(args.steps):
+        r.render_frame_device(intr, poses[(args.warmup + i) % len(poses)])
+        rounds.append(int(r.stats().n_rounds))
+    st = r.stats()
+    rays = W * H
+    out = {"metric": "rays_per_second_1080p" if args.workload == "C3" else f"rays_per_second_{args.workload}",
+           "value": rays * args.steps / (ms_dev * 1e-3), "unit": "rays/s", "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f16",
+           "data": "synthetic",
+           "config": {"workload": f"{args.workload}: {W}x{H} frame, bound {sc.desc.bound:g}, {sc.desc.cascades} cascades, log2_hashmap_size "
+                                  f"{sc.desc.log2_hashmap_size}, base.json MLPs, random-init weights, synthetic occupancy, {len(poses)} orbit poses cycled",
+                      "mode": "inproc: one process, nrf_create(n_gpus) — the ngp::NerfRender(n) / render_server --gpus n path",
+                      "sharding": f"32x32-pixel tiles round-robin over {n} devices of one process; every device's composite kernel stores its u8 "
+                                  f"pixels into device 0's frame over NVLink (peer access), device 0 waits on the other devices' events; no collective",
+                      "scene": args.scene, "samples_per_frame": float(st.n_samples), "samples_per_ray": float(st.n_samples) / rays,
+                      "l2": "inputs larger than L2 (see the default mode's line); the pose changes every step"},
+           "e2e": {"value": rays * args.steps / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
+                   "batch_call_value": batch_rps, "h2d_bytes_per_step": 80, "d2h_bytes_per_step": rays * 4 + 8 * n,
+                   "note": "value: nrf_render_frame per pose (returns the host frame, one sync per frame); batch_call_value: the same poses "
+                           "through nrf_render_batch (frame i's D2H on a copy stream beside frame i+1's kernels), wall clock"},
+           "gpu_launches": 5 * int(sum(rounds)) * n, "overflowed_timed_frames": int(ovf), "clocks": clocks,
+           "frame_breakdown_ms_device0": {"rays+count+scan": st.ms_setup, "emit": st.ms_march, "network": st.ms_network,
+                                          "composite": st.ms_composite, "total": st.ms_total}}
+    print(json.dumps(out), flush=True)
+    r.close()
+
+
+def reference_arm(args):
+    """--impl reference.  The reference has no CPU implementation of this path — it IS a CUDA renderer — so the arm runs
+    the reference's own CUDA code (baseline/_ref, built from /root/reference by baseline/build_ref_cuda.sh) on GPU 0 of
+    this box when the binary travelled here; the CPU port (oracle/) is timed beside it as cpu_baseline, and is the arm
+    itself only where the binary or a GPU is missing.  The reference's GPU count is a compile-time constant (NGPU,
+    common.h:91; built with 1), so for --gpus N > 1 the line is still its single-GPU number and says so."""
+    cfg, W, H, _ = WORKLOADS[args.workload]
+    metric = "rays_per_second_1080p" if args.workload == "C3" else f"rays_per_second_{args.workload}"
+    steps, warm = max(1, args.steps), max(0, args.warmup)
+    base = {"impl": "reference", "metric": metric, "unit": "rays/s", "n_gpus": args.gpus, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f16", "data": "synthetic"}
+    g = ref_cuda_arm(args.workload, steps, warm, "ref_cuda_driver_d1")
+    if g and "error" not in g:
+        shipped = ref_cuda_arm(args.workload, max(2, min(steps, 8)), min(warm, 2), "ref_cuda_driver")
+        c = None if args.no_cpu else cpu_arm(args.workload, steps=2, warmup=1, target_s=4.0)
+        return {**base, "value": g["value"], "steps": steps, "warmup": warm, "ms_per_step": g["ms_per_step"],
+                "config": {"workload": f"{args.workload}: {W}x{H} frame, same model, occupancy grid and {WORKLOADS[args.workload][3]} orbit poses as "
+                                       f"the default arm, handed over as a .msgpack snapshot",
+                           "implementation": "the reference's own CUDA renderer (src/nerf_render.cu + tiny-cuda-nn, compiled for sm_100 by "
+                                             "baseline/build_ref_cuda.sh), NerfRender::render_frame on ONE GPU (NGPU is a compile-time constant)",
+                           "variant": "D1-clean: one cudaMemsetAsync of the deltas buffer before the march so no uninitialised samples are "
+                                      "evaluated (SURVEY.md defect D1) — the FASTER of the two builds, i.e. the conservative baseline; "
+                                      "`as_shipped` is the unmodified source"},
+                "as_shipped": None if not shipped or "error" in shipped else
+                              {"value": shipped["value"], "ms_per_step": shipped["ms_per_step"], "unit": "rays/s"},
+                "load_seconds": g["load_s"],
+                "cpu_baseline": ({"value": c["value"], "unit": "rays/s", "cores": c["cores"], "kind": "port", "sample": c["sample"]} if c else None),
+                "e2e": {"value": g["value"], "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                        "note": "render_frame itself takes a host pose and returns the host u8 frame: value is already end to end"}}
+    steps, warm = min(steps, 8), min(warm, 2)
+    c = cpu_arm(args.workload, steps=steps, warmup=warm, target_s=6.0)
+    return {**base, "value": c["value"], "steps": steps, "warmup": warm, "ms_per_step": c["ms_per_step"],
+            "config": {"workload": f"{args.workload}: {W}x{H} frame (CPU arm renders a bounded row band per step)",
+                       "implementation": "CPU port of the reference's path (oracle/, OpenMP over rays): "
+                                         + (g["error"] if g else "baseline/_ref/ref_cuda_driver_d1 or a GPU is not present")},
+            "cpu_baseline": {"value": c["value"], "unit": "rays/s", "cores": c["cores"], "kind": "port", "sample": c["sample"]},
+            "e2e": {"value": c["value"], "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -352,26 +562,28 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--gather", default="nccl", choices=["peer", "nccl"],
-                    help="N>1: nccl = gather of packed u8 tiles to rank 0 (default: measured 3 %% faster, the non-root ranks are not "
-                         "held in lockstep); peer = composite kernels store into rank 0's frame over NVLink, 4-byte all-reduce fence")
+    ap.add_argument("--scene", default="random", choices=["random", "opaque"],
+                    help="random = random-init weights (BASELINE.json's config: semi-transparent fog, nothing terminates early); opaque = same "
+                         "model with the density head scaled so rays saturate after a few samples (a trained scene's behaviour)")
+    ap.add_argument("--mode", default="ranks", choices=["ranks", "inproc"],
+                    help="N>1: ranks (default) = one process per GPU (torchrun); inproc = one process drives all N GPUs through "
+                         "nrf_create(N), the path render_server --gpus N uses")
+    ap.add_argument("--shard", default="tiles", choices=["tiles", "poses"],
+                    help="N>1: tiles (default) = every rank renders its 32x32-pixel tiles of the SAME frame (strong scaling, latency); "
+                         "poses = rank k renders whole frames of poses k, k+N, ... (throughput; no intra-frame traffic)")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="N>1: peer (default) = composite kernels store into rank 0's frame over NVLink, one-sided sequence-flag fence, "
+                         "no collective; nccl = gather of packed u8 tiles to rank 0 + tile transpose (the round-1 path)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) != 0:
             return
-        cfg, W, H, _ = WORKLOADS[args.workload]
-        steps, warm = min(args.steps, 8), min(args.warmup, 2)
-        c = cpu_arm(args.workload, steps=steps, warmup=warm, target_s=6.0)
-        print(json.dumps({
-            "impl": "reference", "metric": "rays_per_second_1080p" if args.workload == "C3" else f"rays_per_second_{args.workload}",
-            "value": c["value"], "unit": "rays/s", "n_gpus": args.gpus, "steps": steps, "warmup": warm,
-            "ms_per_step": c["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f16",
-            "data": "synthetic", "config": {"workload": f"{args.workload}: {W}x{H} frame (CPU arm renders a bounded row band per step)"},
-            "cpu_baseline": {"value": c["value"], "unit": "rays/s", "cores": c["cores"], "kind": "port", "sample": c["sample"]},
-            "e2e": {"value": c["value"], "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "note": "CPU port of the reference's path (oracle/, OpenMP over rays); the reference's own CUDA build needs "
-                    "cmake + CUDA-11 APIs and is recorded as unbuildable here (DESIGN.md)"}))
+        print(json.dumps(reference_arm(args)), flush=True)
+        return
+    if args.mode == "inproc" and args.gpus > 1:
+        if int(os.environ.get("RANK", "0")) == 0:   # under torchrun the other ranks have nothing to do
+            inproc_arm(args)
         return
     gpu_arm(args)
 

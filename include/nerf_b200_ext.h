@@ -30,23 +30,37 @@ int nrf_stream(nrf_ctx* ctx, void** stream);
 int nrf_shard_pixel(nrf_ctx* ctx, int q, int* pixel);
 
 /* ---- peer frame: the gather fused into the composite kernel (one process per GPU) ---------------------------------
- * The destination rank exports ONE buffer holding two frames used alternately (each: rgb W*H*3 bytes followed by depth
- * W*H bytes, pixel order) as a 64-byte CUDA IPC handle; every other rank attaches it.  Frames alternate so that the
- * destination may still be copying frame i out while the others store frame i+1: with one fence per frame, the fence of
- * frame i+1 orders the end of that copy before anyone stores frame i+2.  Every rank must render every frame.  From then on each rank's composite kernel stores its u8 pixels
- * straight into that buffer over NVLink (peer stores), so no collective moves pixels: the caller only needs a
- * completion fence (any stream-ordered collective, or a barrier after nrf_synchronize) before the destination reads.
+ * The destination rank ("owner") exports ONE buffer holding two frames used alternately (each: rgb W*H*3 bytes followed
+ * by depth W*H bytes, pixel order) plus a few 32-bit sequence flags, as a 64-byte CUDA IPC handle; every other rank
+ * attaches it.  From then on each rank's composite kernel stores its u8 pixels straight into that buffer over NVLink (peer
+ * stores): no collective moves pixels, and none orders them either — the completion fence is ONE-SIDED.  After its composite
+ * of frame k every rank's stream stores k into its own flag (st.release.sys); the owner's copy stream waits until every
+ * flag has reached k (a one-warp kernel polling with ld.acquire.sys), copies the slot to the host if asked to, and
+ * publishes ack = k; a rank waits for ack >= k-2 before its composite overwrites the slot frame k-2 was in, so the owner
+ * may still be copying frame k-1 out while everybody renders frame k.  Ranks are never held in lockstep and no rank waits
+ * for a frame it does not write.  Every rank must render every frame (frames are counted, not named).  A wait gives up
+ * after 20 s and the owner's next sync point fails instead of hanging the GPU.
  * The exporting context writes into its own buffer directly.  Call after nrf_set_shard + nrf_set_resolution; detach
- * before changing either.  A frame whose samples do not fit the context's buffers is re-rendered at that rank's next
- * host sync point (nrf_synchronize, ...): either synchronise every rank before the fence, or — as bench.py does — size
- * the buffers with one untimed pass over the poses first, after which a stream-ordered fence alone is enough.  (Reference: host threads + 2 D2H copies per GPU + CPU re-interleave, nerf_render.cu:345-358.) */
+ * before changing either.  A frame whose samples do not fit a rank's buffers is re-rendered at that rank's next host sync
+ * point, which the owner cannot see: size the buffers with an untimed pass over the poses first (as bench.py does; frames
+ * that overflowed are counted by nrf_overflowed_frames).
+ * (Reference: host threads + 2 D2H copies per GPU + CPU re-interleave, nerf_render.cu:345-358.) */
 int nrf_peer_frame_export(nrf_ctx* ctx, void* handle64);
 int nrf_peer_frame_attach(nrf_ctx* ctx, const void* handle64);
 int nrf_peer_frame_detach(nrf_ctx* ctx);
-/* Destination rank: device pointer of the frame; async copy to context-owned pinned memory on the context's stream
- * (synchronise before reading *rgb / *depth, which stay valid until detach / destroy). */
+/* Owner: device pointer of the latest frame's slot. */
 int nrf_peer_frame_device(nrf_ctx* ctx, void** frame);
+/* Owner: the latest frame in context-owned pinned memory, complete (every rank's fence passed) when the call returns. */
 int nrf_peer_frame_to_host(nrf_ctx* ctx, uint8_t** rgb, uint8_t** depth);
+/* Owner: copy every later frame to the host behind its fence, on the copy stream, overlapping the next frame (two pinned
+ * slots); nrf_peer_frame_collect(back) then returns frame (latest - back), back = 0 or 1, waiting only for that frame.  On
+ * the other ranks collect waits for the rank's own kernels of that frame and returns NULL pointers. */
+int nrf_peer_frame_copy_out(nrf_ctx* ctx, int on);
+int nrf_peer_frame_collect(nrf_ctx* ctx, int back, uint8_t** rgb, uint8_t** depth);
+/* Make device 0's stream wait for whatever the latest frame still has in flight elsewhere: the other devices' kernels (one
+ * process, several devices) and, on the owner of a peer frame, that frame's fence.  An event recorded on nrf_stream()
+ * afterwards covers the whole frame. */
+int nrf_frame_join(nrf_ctx* ctx);
 
 /* Asynchronous device frames (nrf_render_frame_device without a sync in between) whose samples did not fit the sample
  * buffers: such a frame is rendered incompletely; the LATEST one is re-rendered at the next sync point, earlier ones

@@ -207,11 +207,24 @@ class NerfRender:
         return p.value
 
     def peer_frame_to_host(self):
-        """Async copy on the context's stream; returns (rgb[H,W,3], depth[H,W]) views — synchronize() before reading."""
+        """Owner: the latest frame on the host, complete when the call returns; (rgb[H,W,3], depth[H,W]) views."""
+        return self.peer_frame_collect(0)
+
+    def peer_frame_copy_out(self, on=True):
+        _check(self._l.nrf_peer_frame_copy_out(self._ctx, int(bool(on))))
+
+    def peer_frame_collect(self, back=0):
+        """Owner: frame (latest - back) as (rgb[H,W,3], depth[H,W]) views of pinned memory; other ranks: waits for the rank's
+        own latest frame and returns None."""
         rgb, dep = C.POINTER(C.c_ubyte)(), C.POINTER(C.c_ubyte)()
-        _check(self._l.nrf_peer_frame_to_host(self._ctx, C.byref(rgb), C.byref(dep)))
+        _check(self._l.nrf_peer_frame_collect(self._ctx, int(back), C.byref(rgb), C.byref(dep)))
+        if not rgb:
+            return None
         W, H = self.W, self.H
         return (np.ctypeslib.as_array(rgb, shape=(H, W, 3)), np.ctypeslib.as_array(dep, shape=(H, W)))
+
+    def frame_join(self):
+        _check(self._l.nrf_frame_join(self._ctx))
 
     def bench_stage(self, what, n=0, iters=5) -> float:
         ms = C.c_float()

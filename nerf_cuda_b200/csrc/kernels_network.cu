@@ -147,7 +147,8 @@ __device__ __forceinline__ float2 mul2(float2 v, float w) {
 // One level of tcnn kernel_grid (grid.h:186-268) + grid_index/fast_hash (grid.h:81-117): trilinear blend accumulated
 // in fp16 in corner order 0..7 (corner bit d selects g[d]+1 and weight w[d], else 1-w[d]; weight = (f0*f1)*f2).
 // Index math: hashed levels  (x ^ y*2654435761 ^ z*805459861) & (T-1)   (T is a power of two);
-//             dense levels   x + y*res + z*res^2, which is < 2T, so min(a, a-T) (unsigned) equals the reference's % T.
+//             dense levels   x + y*res + z*res^2, which is < 2T, so min(a, a-T) (unsigned) equals the reference's % T;
+//             mode 3         the same dense index in wrapping 32-bit arithmetic & (T-1), where the reference's stride overflowed.
 // Straight-line code, no divergence.  On hashed levels the two x-corners of a cell share an aligned 8-byte slot exactly
 // when x is even (the hash prime for x is 1, grid.h:88): one LDG.64 fetches the slot of the x corner and a LDG.32
 // predicated on "x odd" fetches the x+1 corner when it lives elsewhere; the predicate is the same for all four pairs.
@@ -199,6 +200,18 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
     for (int j = 0; j < 4; ++j) {
       e[2 * j] = (g0 ^ yz[j]) & m;
       e[2 * j + 1] = (g0p ^ yz[j]) & m;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) T.raw[k] = __ldg(tl + e[k]);
+  } else if (lv.hashed == 3) {
+    // res^3 wrapped below T in the reference's 32-bit stride (grid.h:100-117): dense index, 32-bit wrap, mod T (a power of 2)
+    const uint32_t r1 = lv.res, r2 = lv.res * lv.res, m = lv.size - 1u;
+    const uint32_t b = g0 + g1 * r1 + g2 * r2;
+    const uint32_t off[4] = {0u, r1, r2, r1 + r2};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      e[2 * j] = (b + off[j]) & m;
+      e[2 * j + 1] = (b + off[j] + 1u) & m;
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) T.raw[k] = __ldg(tl + e[k]);

@@ -180,7 +180,7 @@ static void pack_weight(const float* W, int n_out, int n_in, uint16_t* dst) {
 // ---------------------------------------------------------------------------------------------------- context
 #define NRF_MAX_ROUNDS 4
 // device counters of a frame (Device::total; written by k_scan_blocks / k_rays_count / k_composite)
-enum { TOT_ROUND = 0, TOT_MAX = 1, TOT_OVF_EVENTS = 2, TOT_MARCHED = 3, TOT_EVAL = 4, TOT_USED = 5, TOT_FRAME_OVF = 6, TOT_N = 8 };
+enum { TOT_ROUND = 0, TOT_MAX = 1, TOT_OVF_EVENTS = 2, TOT_MARCHED = 3, TOT_EVAL = 4, TOT_USED = 5, TOT_FRAME_OVF = 6, TOT_PEER_TIMEOUT = 7, TOT_N = 8 };
 
 template <typename T>
 struct DevBuf {
@@ -264,11 +264,22 @@ struct nrf_ctx {
   uint8_t* peer_frame = nullptr;  // device pointer valid in THIS process (own allocation or IPC mapping)
   bool peer_owned = false, peer_mapped = false;
   int peer_slot = 0;              // the buffer holds TWO frames used alternately (see nrf_peer_frame_export)
-  uint8_t* peer_host = nullptr;   // pinned W*H*4, destination rank only
+  unsigned peer_seq = 0;          // frames rendered into the peer frame so far (slot = seq & 1); equal on every rank
+  uint8_t* peer_host = nullptr;   // pinned 2 x W*H*4 (one per slot), destination rank only
+  // one-sided completion fence (no collective): 32-bit sequence numbers behind the two frames.  Rank r's stream stores
+  // `seq` into stored[r] (release, system scope) after its composite of frame `seq`; the owner's copy stream waits for
+  // every stored[r] >= seq, copies the frame out if asked to, then publishes ack = seq; a rank waits for ack >= seq - 2
+  // before its composite overwrites the slot frame seq - 2 was in.
+  cudaStream_t peer_copy_stream = nullptr;   // owner only: fence wait + D2H run here, beside the next frame's kernels
+  cudaEvent_t peer_copied[2] = {nullptr, nullptr};   // owner: slot consumed (recorded on peer_copy_stream)
+  bool peer_copied_valid[2] = {false, false};
+  cudaEvent_t peer_done[2] = {nullptr, nullptr};     // every rank: this rank's own kernels of the frame in that slot finished
+  bool peer_copy_out = false;     // owner: copy every frame to peer_host[slot] behind the fence
   uint8_t* rgb_host = nullptr;    // pinned, W*H*3 (full frame when n_shards == 1, else this shard's packed tiles)
   uint8_t* depth_host = nullptr;  // pinned, W*H
   uint8_t* batch_stage[2] = {nullptr, nullptr};   // pinned staging of nrf_render_batch's two-deep pipeline
   cudaEvent_t batch_ev[2] = {nullptr, nullptr};
+  cudaStream_t batch_copy_stream = nullptr;   // device 0: the frame's D2H runs here, beside the next frame's kernels
   // set while nrf_render_batch pipelines frames on several devices: the event after which device 0's frame may be
   // overwritten (its copy to the staging buffer has finished); the other devices' pixel-writing composite waits on it
   cudaEvent_t pixel_wait = nullptr;
@@ -286,6 +297,7 @@ static int device_count() {
 }
 
 struct nrf_ctx;
+static int peer_detach(nrf_ctx* c);
 static int frame_resolve(nrf_ctx* c);  // host sync point of an asynchronously enqueued frame (defined with the frame code)
 
 extern "C" int nrf_create(int n_gpus, const int* device_ids, nrf_ctx** out) {
@@ -341,13 +353,10 @@ extern "C" int nrf_destroy(nrf_ctx* c) {
   if (!c) return NRF_OK;
   c->pending = false;
   for (Device& D : c->devs) { cudaSetDevice(D.dev); if (D.stream) cudaStreamSynchronize(D.stream); }
-  if (c->peer_frame) {
-    cudaSetDevice(c->devs[0].dev);
-    cudaStreamSynchronize(c->devs[0].stream);
-    if (c->peer_mapped) cudaIpcCloseMemHandle(c->peer_frame);
-    else if (c->peer_owned) cudaFree(c->peer_frame);
-  }
+  if (c->peer_frame) peer_detach(c);
   if (c->peer_host) cudaFreeHost(c->peer_host);
+  cudaSetDevice(c->devs[0].dev);
+  if (c->batch_copy_stream) { cudaStreamSynchronize(c->batch_copy_stream); cudaStreamDestroy(c->batch_copy_stream); }
   for (int k = 0; k < 2; ++k) {
     if (c->batch_stage[k]) cudaFreeHost(c->batch_stage[k]);
     if (c->batch_ev[k]) cudaEventDestroy(c->batch_ev[k]);
@@ -420,15 +429,23 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
     L.size = c->levels.offsets[l + 1] - c->levels.offsets[l];
     L.res = c->levels.res[l];
     L.scale = c->levels.scales[l];
-    // grid_index (grid.h:100-117): hash iff T_l < res^3 (the stride loop stops early instead of overflowing)
+    // grid_index (grid.h:100-117) decides in 32-bit arithmetic: stride *= res for every dimension while stride <= T_l,
+    // then "hash iff T_l < stride".  The early stop keeps most fine levels from overflowing, but when res^2 <= T_l < res^3
+    // the third multiplication can still wrap below T_l (res 2048 at T = 2^22..2^24: stride = 2^33 -> 0; res 2581 at
+    // bound 16): the reference then uses the WRAPPED dense index (x + y*res + z*res^2) mod T_l instead of the hash.
+    // Followed as is (mode 3) — the reference's exported tables were trained with exactly that addressing.
+    uint32_t stride = 1, dims = 0;
+    for (; dims < 3 && stride <= L.size; ++dims) stride *= L.res;
+    const bool ref_hashed = L.size < stride;
     const double dense = (double)L.res * L.res * L.res;
-    L.hashed = dense > (double)L.size ? 1u : 0u;
+    L.hashed = ref_hashed ? 1u : (dense > (double)L.size ? 3u : 0u);
+    if (L.hashed == 3u && dims != 3) return fail(NRF_EINVAL, "level %u (res %u, size %u): unsupported index overflow", l, L.res, L.size);
     if (L.hashed && (L.size & (L.size - 1)) != 0) return fail(NRF_EINVAL, "hashed level %u size %u not a power of two", l, L.size);
     // hashed levels below pair_from use plain 4-byte loads (2), from pair_from on the paired 8-byte slot loads (1)
     // (measured on B200: C3 network 5.68 / 5.62 / 5.69 / 5.78 ms at pair_from 0 / 8 / 12->5.57 / 16; C2 prefers 16 by 3 %:
     // pairing trades ~5 instructions per corner pair for fewer L1 wavefronts, which pays only on the finest levels)
     static const int pair_from = std::getenv("NRF_PAIR_FROM") ? std::atoi(std::getenv("NRF_PAIR_FROM")) : 12;
-    if (L.hashed && (int)l < pair_from) L.hashed = 2u;
+    if (L.hashed == 1u && (int)l < pair_from) L.hashed = 2u;
   }
   N.mlp_rowmaj = D.params_h.p;
   N.table = reinterpret_cast<const __half2*>(D.params_h.p + 10240);
@@ -673,6 +690,7 @@ extern "C" int nrf_synchronize(nrf_ctx* c) {
     CU(cudaSetDevice(D.dev));
     CU(cudaStreamSynchronize(D.stream));
   }
+  if (c->peer_copy_stream) CU(cudaStreamSynchronize(c->peer_copy_stream));
   return NRF_OK;
 }
 
@@ -697,6 +715,46 @@ static int network_grid(nrf_ctx*, const Device& D, int n_samples) {
 }
 
 static inline uint8_t* peer_slot_ptr(nrf_ctx* c) { return c->peer_frame + (size_t)c->peer_slot * c->W * c->H * 4; }
+
+// ---- one-sided fence of the peer frame (see nrf_ctx::peer_seq) ----
+#define NRF_PEER_MAX_RANKS 64
+#define NRF_PEER_FLAG_STRIDE 8   // 32-bit words between two ranks' flags (one 32-byte sector each)
+static inline unsigned* peer_flags(nrf_ctx* c) {
+  const size_t frames = ((size_t)c->W * c->H * 4 * 2 + 255) & ~(size_t)255;
+  return reinterpret_cast<unsigned*>(c->peer_frame + frames);
+}
+static inline size_t peer_alloc_bytes(nrf_ctx* c) {
+  return (((size_t)c->W * c->H * 4 * 2 + 255) & ~(size_t)255) + (NRF_PEER_MAX_RANKS + 1) * NRF_PEER_FLAG_STRIDE * 4;
+}
+static inline unsigned* peer_stored_flag(nrf_ctx* c, int rank) { return peer_flags(c) + (size_t)rank * NRF_PEER_FLAG_STRIDE; }
+static inline unsigned* peer_ack_flag(nrf_ctx* c) { return peer_flags(c) + (size_t)NRF_PEER_MAX_RANKS * NRF_PEER_FLAG_STRIDE; }
+
+// everything this stream wrote before (the composite's pixel stores, local or over NVLink) is visible system-wide before
+// the flag is
+__global__ void k_peer_signal(unsigned* flag, unsigned seq) {
+  __threadfence_system();
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(seq) : "memory");
+}
+// lane i polls flags[(first + i) * stride] until it has reached `seq` (wrap-safe); gives up after timeout_ns and raises the
+// device counter TOT_PEER_TIMEOUT instead of hanging the GPU when a rank died
+__global__ void k_peer_wait(const unsigned* flags, int first, int n, unsigned seq, unsigned long long timeout_ns,
+                            unsigned long long* timed_out) {
+  const int i = threadIdx.x;
+  if (i >= n) return;
+  const unsigned* f = flags + (size_t)(first + i) * NRF_PEER_FLAG_STRIDE;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+    if ((int)(v - seq) >= 0) break;
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    if (t - t0 > timeout_ns) { atomicAdd(timed_out, 1ull); break; }
+    __nanosleep(200);
+  }
+}
+static const unsigned long long kPeerTimeoutNs = 20ull * 1000 * 1000 * 1000;
 
 // One frame on one device, enqueued WITHOUT a host round trip: rays + count + scan leave the sample total in device
 // memory, k_emit / k_network / k_composite read it there; the sample buffers keep the capacity of earlier frames.
@@ -768,8 +826,13 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
                           D.ray_sh.p, 0, nullptr, D.sample_out.p, nullptr, D.total.p + TOT_ROUND, &src));
     CU(cudaEventRecord(r == 0 ? D.ev[3] : D.rev[r][2], D.stream));
     if (D.n_local > 0) {
-      // peer stores into device 0's frame must not overtake the copy-out of the previous frame (nrf_render_batch)
-      if (R.last && c->pixel_wait && &D != &D0) CU(cudaStreamWaitEvent(D.stream, c->pixel_wait, 0));
+      // stores into device 0's frame must not overtake the copy-out of the previous frame, which runs on the copy
+      // stream beside this frame's kernels (nrf_render_batch)
+      if (R.last && c->pixel_wait) CU(cudaStreamWaitEvent(D.stream, c->pixel_wait, 0));
+      if (R.last && c->peer_frame && c->peer_seq > 2) {   // the slot still holds frame seq - 2: wait until it was consumed
+        if (c->peer_owned) { if (c->peer_copied_valid[c->peer_slot]) CU(cudaStreamWaitEvent(D.stream, c->peer_copied[c->peer_slot], 0)); }
+        else k_peer_wait<<<1, 32, 0, D.stream>>>(peer_ack_flag(c), 0, 1, c->peer_seq - 2, kPeerTimeoutNs, D.total.p + TOT_PEER_TIMEOUT);
+      }
       k_composite<<<nb, 128, 0, D.stream>>>(D.n_local, D.map, D.warp_base.p, D.counts.p, D.rays.p, D.far_tf.p, src,
                                             D.sample_out.p, D.rgb_f32.p, D.depth_f32.p, D.used.p, rgb_dst, dep_dst,
                                             u8_pixel_order, R, D.total.p + TOT_USED);
@@ -777,9 +840,34 @@ static int frame_enqueue(nrf_ctx* c, Device& D, const float intr[4], const float
     }
     CU(cudaEventRecord(r == 0 ? D.ev[4] : D.rev[r][3], D.stream));
   }
+  if (c->peer_frame && !c->peer_owned) {   // this rank's pixels of frame peer_seq are in the owner's buffer
+    k_peer_signal<<<1, 1, 0, D.stream>>>(peer_stored_flag(c, c->shard), c->peer_seq);
+    CU(cudaGetLastError());
+  }
   ++D.frame_no;
   CU(cudaMemcpyAsync(D.total_h + TOT_N * (D.frame_no & 3u), D.total.p, TOT_N * sizeof(unsigned long long), cudaMemcpyDeviceToHost, D.stream));
   CU(cudaEventRecord(D.done, D.stream));
+  if (c->peer_frame) CU(cudaEventRecord(c->peer_done[c->peer_slot], D.stream));
+  if (c->peer_frame && c->peer_owned) {
+    // owner: behind its own composite, on the copy stream (so the next frame's kernels are not held up): wait for every
+    // other rank's flag, copy the frame out if asked to, release the slot
+    cudaStream_t cs = c->peer_copy_stream;
+    CU(cudaStreamWaitEvent(cs, D.done, 0));
+    k_peer_signal<<<1, 1, 0, cs>>>(peer_stored_flag(c, c->shard), c->peer_seq);   // the owner's own pixels
+    if (c->n_shards > 1) {
+      for (int first = 0; first < c->n_shards; first += 32)
+        k_peer_wait<<<1, 32, 0, cs>>>(peer_flags(c), first, std::min(32, c->n_shards - first), c->peer_seq, kPeerTimeoutNs,
+                                      D.total.p + TOT_PEER_TIMEOUT);
+      CU(cudaGetLastError());
+    }
+    if (c->peer_copy_out)
+      CU(cudaMemcpyAsync(c->peer_host + (size_t)c->peer_slot * c->W * c->H * 4, peer_slot_ptr(c), (size_t)c->W * c->H * 4,
+                         cudaMemcpyDeviceToHost, cs));
+    k_peer_signal<<<1, 1, 0, cs>>>(peer_ack_flag(c), c->peer_seq);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(c->peer_copied[c->peer_slot], cs));
+    c->peer_copied_valid[c->peer_slot] = true;
+  }
   return NRF_OK;
 }
 
@@ -803,6 +891,8 @@ static int frame_check(nrf_ctx*, Device& D, bool& redo) {
     CU(D.samples.ensure(want)); CU(D.t0rec.ensure(want)); CU(D.sample_out.ensure(want));
   }
   if (slot[TOT_FRAME_OVF]) redo = true;   // a round of the LATEST frame did not fit
+  if (slot[TOT_PEER_TIMEOUT]) return fail(NRF_ECUDA, "peer frame fence timed out (%llu waits): a rank of the job did not deliver its pixels",
+                                          slot[TOT_PEER_TIMEOUT]);
   return NRF_OK;
 }
 
@@ -841,7 +931,7 @@ static int frame_resolve(nrf_ctx* c) {
       if (rc) { c->pending = false; return rc; }
     }
     // termination-aware rounds, decided from the frame just validated (both counts are schedule-independent)
-    if (c->term_mode == 2) {
+    if (c->term_mode == 2 && !redo) {   // (a frame that overflowed composited only part of its samples: no basis for the ratio)
       unsigned long long marched = 0, used = 0;
       for (Device& D : c->devs) { marched += D.last_marched; used += D.last_used; }
       if (marched > 0) {
@@ -864,7 +954,7 @@ static int render_common(nrf_ctx* c, const float intr[4], const float* pose, boo
   // No host sync here: an earlier asynchronous frame that is still unvalidated is superseded (its buffers are reused
   // in stream order; its total stays in the ring as a growth hint for the next sync point).
   int rc;
-  c->peer_slot ^= 1;           // every rank renders every frame, so all ranks alternate in step
+  c->peer_slot = (int)(++c->peer_seq & 1u);   // every rank renders every frame, so all ranks alternate in step
   rc = frame_enqueue_all(c, intr, pose, to_host);
   if (rc) return rc;
   c->pending = true;
@@ -917,6 +1007,7 @@ extern "C" int nrf_render_batch_rgbd(nrf_ctx* c, const float intr[4], const floa
     }
     c->batch_bytes = stage_bytes;
   }
+  if (!c->batch_copy_stream) CU(cudaStreamCreateWithFlags(&c->batch_copy_stream, cudaStreamNonBlocking));
   std::vector<int> redo;
   unsigned fno[2][8] = {};   // per staging slot: frame_no of every device when the frame was enqueued
   auto collect = [&](int j) -> int {   // frame j has landed in staging slot j & 1
@@ -934,19 +1025,19 @@ extern "C" int nrf_render_batch_rgbd(nrf_ctx* c, const float intr[4], const floa
   for (int i = 1; i < n_poses; ++i) {
     const int slot = i & 1;
     if (i >= 3) { rc = collect(i - 2); if (rc) return rc; }   // frees this staging slot
-    c->peer_slot ^= 1;
+    c->peer_slot = (int)(++c->peer_seq & 1u);
     // frame i-1's copy out of device 0's frame (recorded in batch_ev[(i-1)&1]) must finish before another device's
     // composite stores frame i's pixels there; frame 0 was rendered synchronously
-    c->pixel_wait = i >= 2 ? c->batch_ev[(i - 1) & 1] : nullptr;
+    c->pixel_wait = i >= 2 ? c->batch_ev[(i - 1) & 1] : nullptr;   // (frame 1: frame 0 was copied synchronously)
     rc = frame_enqueue_all(c, intr, poses + (size_t)i * 16, false);
     c->pixel_wait = nullptr;
     if (rc) return rc;
     for (size_t g = 0; g < c->devs.size() && g < 8; ++g) fno[slot][g] = c->devs[g].frame_no;
     CU(cudaSetDevice(D0.dev));
-    for (size_t g = 1; g < c->devs.size(); ++g) CU(cudaStreamWaitEvent(D0.stream, c->devs[g].done, 0));
-    CU(cudaMemcpyAsync(c->batch_stage[slot], D0.rgb_u8.p, frame_bytes, cudaMemcpyDeviceToHost, D0.stream));
-    if (depth_out) CU(cudaMemcpyAsync(c->batch_stage[slot] + frame_bytes, D0.depth_u8.p, px, cudaMemcpyDeviceToHost, D0.stream));
-    CU(cudaEventRecord(c->batch_ev[slot], D0.stream));
+    for (size_t g = 0; g < c->devs.size(); ++g) CU(cudaStreamWaitEvent(c->batch_copy_stream, c->devs[g].done, 0));
+    CU(cudaMemcpyAsync(c->batch_stage[slot], D0.rgb_u8.p, frame_bytes, cudaMemcpyDeviceToHost, c->batch_copy_stream));
+    if (depth_out) CU(cudaMemcpyAsync(c->batch_stage[slot] + frame_bytes, D0.depth_u8.p, px, cudaMemcpyDeviceToHost, c->batch_copy_stream));
+    CU(cudaEventRecord(c->batch_ev[slot], c->batch_copy_stream));
     c->pending = true;
     c->pending_to_host = false;
     std::memcpy(c->pending_intr, intr, 16);
@@ -1474,10 +1565,24 @@ static int peer_detach(nrf_ctx* c) {
   if (!c->peer_frame) return NRF_OK;
   CU(cudaSetDevice(c->devs[0].dev));
   CU(cudaStreamSynchronize(c->devs[0].stream));
+  if (c->peer_copy_stream) {
+    CU(cudaStreamSynchronize(c->peer_copy_stream));
+    CU(cudaStreamDestroy(c->peer_copy_stream));
+    c->peer_copy_stream = nullptr;
+  }
+  for (int k = 0; k < 2; ++k) {
+    if (c->peer_copied[k]) CU(cudaEventDestroy(c->peer_copied[k]));
+    if (c->peer_done[k]) CU(cudaEventDestroy(c->peer_done[k]));
+    c->peer_copied[k] = c->peer_done[k] = nullptr;
+    c->peer_copied_valid[k] = false;
+  }
   if (c->peer_mapped) CU(cudaIpcCloseMemHandle(c->peer_frame));
   else if (c->peer_owned) CU(cudaFree(c->peer_frame));
   c->peer_frame = nullptr;
   c->peer_owned = c->peer_mapped = false;
+  c->peer_copy_out = false;
+  c->peer_seq = 0;
+  c->peer_slot = 0;
   return NRF_OK;
 }
 
@@ -1493,13 +1598,20 @@ extern "C" int nrf_peer_frame_export(nrf_ctx* c, void* handle64) {
   CU(cudaSetDevice(D.dev));
   // TWO frames, written alternately: the destination can still be copying frame i out while the other ranks store
   // frame i+1 — the completion fence of frame i+1 then orders "copy of i finished" before anyone stores frame i+2
-  const size_t bytes = (size_t)c->W * c->H * 4 * 2;
+  if (c->n_shards > NRF_PEER_MAX_RANKS) return fail(NRF_EINVAL, "peer frame supports up to %d ranks", NRF_PEER_MAX_RANKS);
+  const size_t bytes = peer_alloc_bytes(c);   // two frames + the fence flags
   c->peer_slot = 0;
+  c->peer_seq = 0;
   CU(cudaMalloc(&c->peer_frame, bytes));
   c->peer_owned = true;
   CU(cudaMemsetAsync(c->peer_frame, 0, bytes, D.stream));
   CU(cudaStreamSynchronize(D.stream));
-  if (!c->peer_host) CU(cudaMallocHost(&c->peer_host, bytes / 2));
+  if (!c->peer_host) CU(cudaMallocHost(&c->peer_host, (size_t)c->W * c->H * 4 * 2));
+  CU(cudaStreamCreateWithFlags(&c->peer_copy_stream, cudaStreamNonBlocking));
+  for (int k = 0; k < 2; ++k) {
+    CU(cudaEventCreateWithFlags(&c->peer_copied[k], cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->peer_done[k], cudaEventDisableTiming));
+  }
   cudaIpcMemHandle_t h;
   CU(cudaIpcGetMemHandle(&h, c->peer_frame));
   std::memcpy(handle64, &h, 64);
@@ -1521,6 +1633,8 @@ extern "C" int nrf_peer_frame_attach(nrf_ctx* c, const void* handle64) {
   c->peer_frame = (uint8_t*)p;
   c->peer_mapped = true;
   c->peer_slot = 0;
+  c->peer_seq = 0;
+  for (int k = 0; k < 2; ++k) CU(cudaEventCreateWithFlags(&c->peer_done[k], cudaEventDisableTiming));
   return NRF_OK;
 }
 
@@ -1538,14 +1652,58 @@ extern "C" int nrf_peer_frame_device(nrf_ctx* c, void** frame) {
   *frame = peer_slot_ptr(c);
   return NRF_OK;
 }
+// Owner: the LATEST frame on the host.  Waits for the one-sided fence of that frame (every rank's pixels have landed),
+// copies the slot out unless nrf_peer_frame_copy_out already did so behind the fence, and returns when the bytes are there.
 extern "C" int nrf_peer_frame_to_host(nrf_ctx* c, uint8_t** rgb, uint8_t** depth) {
+  return nrf_peer_frame_collect(c, 0, rgb, depth);
+}
+
+// Owner: switch the automatic copy-out on or off: every later frame is copied to its own pinned host slot on the copy
+// stream as soon as the fence of that frame has passed, while the next frame is already rendering.
+extern "C" int nrf_peer_frame_copy_out(nrf_ctx* c, int on) {
   if (!c) return fail(NRF_EINVAL, "null ctx");
   if (!c->peer_frame || !c->peer_owned) return fail(NRF_ESTATE, "not the owner of a peer frame");
-  { int rc_ = frame_resolve(c); if (rc_) return rc_; }   // this rank's own frame must be valid before it is copied
+  c->peer_copy_out = on != 0;
+  return NRF_OK;
+}
+
+// Frame `back` frames before the latest (0 or 1; the buffer holds two).  Owner: waits until that frame's fence has passed
+// and it is on the host, returns pointers into its pinned slot (valid until two more frames have been rendered).  Other
+// ranks: waits until this rank's own kernels of that frame have finished (rgb/depth are set to NULL) — what keeps a rank's
+// host loop from running more than a frame ahead of its GPU.
+extern "C" int nrf_peer_frame_collect(nrf_ctx* c, int back, uint8_t** rgb, uint8_t** depth) {
+  if (!c || back < 0 || back > 1) return fail(NRF_EINVAL, "nrf_peer_frame_collect: bad arguments");
+  if (!c->peer_frame) return fail(NRF_ESTATE, "no peer frame");
   Device& D = c->devs[0];
   CU(cudaSetDevice(D.dev));
-  CU(cudaMemcpyAsync(c->peer_host, peer_slot_ptr(c), (size_t)c->W * c->H * 4, cudaMemcpyDeviceToHost, D.stream));
-  if (rgb) *rgb = c->peer_host;
-  if (depth) *depth = c->peer_host + (size_t)c->W * c->H * 3;
+  if (rgb) *rgb = nullptr;
+  if (depth) *depth = nullptr;
+  if (c->peer_seq <= (unsigned)back) return fail(NRF_ESTATE, "nrf_peer_frame_collect: no such frame yet");
+  const int slot = (int)((c->peer_seq - (unsigned)back) & 1u);
+  if (!c->peer_owned) { CU(cudaEventSynchronize(c->peer_done[slot])); return NRF_OK; }
+  uint8_t* host = c->peer_host + (size_t)slot * c->W * c->H * 4;
+  if (!c->peer_copy_out) {   // not copied behind the fence: do it now, after the slot's fence, on the copy stream
+    if (back != 0) return fail(NRF_ESTATE, "nrf_peer_frame_collect: an earlier frame needs nrf_peer_frame_copy_out");
+    CU(cudaMemcpyAsync(host, c->peer_frame + (size_t)slot * c->W * c->H * 4, (size_t)c->W * c->H * 4, cudaMemcpyDeviceToHost,
+                       c->peer_copy_stream));
+    CU(cudaStreamSynchronize(c->peer_copy_stream));
+  } else {
+    CU(cudaEventSynchronize(c->peer_copied[slot]));
+  }
+  if (back == 0) { int rc_ = frame_resolve(c); if (rc_) return rc_; }   // the latest frame must also be a valid one
+  if (rgb) *rgb = host;
+  if (depth) *depth = host + (size_t)c->W * c->H * 3;
+  return NRF_OK;
+}
+
+// Makes device 0's stream wait for everything the latest frame still has in flight elsewhere — the other devices' kernels
+// (one process, several devices) and the owner's fence of the peer frame (one process per GPU; a no-op on the other
+// ranks) — so that an event recorded on that stream afterwards covers the whole frame: what bench.py brackets.
+extern "C" int nrf_frame_join(nrf_ctx* c) {
+  if (!c) return fail(NRF_EINVAL, "null ctx");
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  for (size_t g = 1; g < c->devs.size(); ++g) CU(cudaStreamWaitEvent(D.stream, c->devs[g].done, 0));
+  if (c->peer_frame && c->peer_owned && c->peer_seq) CU(cudaStreamWaitEvent(D.stream, c->peer_copied[c->peer_seq & 1u], 0));
   return NRF_OK;
 }

@@ -31,7 +31,7 @@ struct LevelInfo {
   uint32_t res;     // grid resolution
   float scale;      // exp2f(l*log2(b))*N_min - 1 evaluated on the DEVICE like the reference's kernel_grid does (grid.h:186;
                     // MUFU.EX2 and glibc's exp2f differ by an ulp on some levels), once at load time (k_level_scales)
-  uint32_t hashed;  // 1 if res^3 > T_l (fast_hash), 0 = dense index
+  uint32_t hashed;  // 0 dense index; 1 fast_hash with paired 8-byte slot loads; 2 fast_hash, 4-byte loads; 3 wrapped dense index & (T-1)
   uint32_t pad;
   const uint32_t* tab;  // first entry of the level (one __half2 = one uint32 per entry): address = tab + index, 1 IMAD.WIDE
 };

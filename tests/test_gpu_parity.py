@@ -164,8 +164,18 @@ def test_frame_parity(pair, az):
     u8_ref = O.to_u8(rgb2).reshape(H, W, 3)
     assert np.abs(rgb_u8.astype(int) - u8_ref.astype(int)).max() <= 2
     assert rgb_u8.shape == (H, W, 3) and dep_u8.shape == (H, W)
+    # sample accounting: the march finds exactly the samples the oracle's march finds; what is evaluated lies between what
+    # is composited and what was marched, and with evaluation rounds off (whole rays) it IS what was marched
+    o, d, nr, fr = O.rays(intr, pose, W, H)
+    marched = int(O.march(o, d, nr, fr, want_samples=False)[0].sum())
     st = r.stats()
-    assert st.n_samples == cnt2.sum() or st.n_samples >= cnt2.sum()
+    assert st.n_samples_marched == marched and st.n_samples_used == int(cnt2.sum())
+    assert marched >= st.n_samples >= int(cnt2.sum())
+    r.set_termination(0)
+    r.render_frame(intr, pose)
+    st = r.stats()
+    r.set_termination(2)
+    assert st.n_samples == marched and st.n_rounds == 1 and st.n_samples_used == int(cnt2.sum())
 
 
 def test_frame_sigmoid_activation(built_lib):
@@ -391,6 +401,83 @@ def test_peer_frame_ipc_two_processes(pair, tmp_path):
     assert np.array_equal(rgb, full_rgb) and np.array_equal(dep, full_dep)
     with pytest.raises(Exception):
         r0.set_resolution((W + 1, H))           # must detach first
+    r0.peer_frame_detach()
+    r0.close()
+
+
+_PEER_PIPE_CHILD = """
+import sys
+sys.path.insert(0, sys.argv[1])
+import numpy as np
+from nerf_cuda_b200 import NerfRender, synthetic as syn
+name, W, H, shard, world, dev, K = sys.argv[2], int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5]), int(sys.argv[6]), int(sys.argv[7]), int(sys.argv[8])
+sc = syn.make_scene(name)
+r = NerfRender(1, device_ids=[dev])
+r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+r.set_shard(shard, world)
+r.set_resolution((W, H))
+intr = syn.intrinsics(W, H)
+poses = [syn.look_at_pose(syn.camera_radius(name), 20.0, 45.0 * k) for k in range(K)]
+for p in poses:                      # size the sample buffers before the peer frame counts frames
+    r.render_frame_device(intr, p)
+r.synchronize()
+r.peer_frame_attach(bytes.fromhex(sys.stdin.readline().strip()))
+for k, p in enumerate(poses):        # no host sync between frames: the ack flag is what holds this rank back
+    r.render_frame_device(intr, p)
+    if k:
+        r.peer_frame_collect(1)
+r.peer_frame_collect(0)
+r.synchronize()
+assert r.overflowed_frames() == 0
+r.peer_frame_detach()
+r.close()
+print("child done")
+"""
+
+
+def test_peer_frame_one_sided_fence_pipeline(pair, tmp_path):
+    """The one-sided fence of the peer frame, two concurrent PROCESSES (on two GPUs where the box has them, else sharing one):
+    K frames are rendered back to back with no collective and no barrier between the ranks; the owner's copy stream waits for
+    the other rank's sequence flag, copies each frame to its own pinned slot and publishes the ack that lets the other rank
+    reuse the slot two frames later.  Every frame the owner collects — one frame behind the one it is rendering — must equal
+    the unsharded frame byte for byte, whichever rank runs ahead."""
+    import subprocess, sys as _sys
+    import torch
+    name, sc, r, O = pair
+    W, H, world, K = 160, 96, 2, 6
+    intr = syn.intrinsics(W, H)
+    poses = [syn.look_at_pose(syn.camera_radius(name), 20.0, 45.0 * k) for k in range(K)]
+    r.set_shard(0, 1)
+    r.set_resolution((W, H))
+    full = [tuple(a.copy() for a in r.render_frame(intr, p)) for p in poses]
+    r0 = NerfRender(1)
+    r0.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    r0.set_shard(0, world)
+    r0.set_resolution((W, H))
+    for p in poses:
+        r0.render_frame_device(intr, p)
+    r0.synchronize()
+    handle = r0.peer_frame_export()
+    r0.peer_frame_copy_out(True)
+    script = tmp_path / "peer_pipe_child.py"
+    script.write_text(_PEER_PIPE_CHILD)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    dev = 1 if torch.cuda.device_count() > 1 else 0
+    child = subprocess.Popen([_sys.executable, str(script), root, name, str(W), str(H), "1", str(world), str(dev), str(K)],
+                             stdin=subprocess.PIPE, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    child.stdin.write(handle.hex() + "\n")
+    child.stdin.flush()
+    got = []
+    for k, p in enumerate(poses):
+        r0.render_frame_device(intr, p)
+        if k:
+            got.append(tuple(a.copy() for a in r0.peer_frame_collect(1)))
+    got.append(tuple(a.copy() for a in r0.peer_frame_collect(0)))
+    out, err = child.communicate(timeout=300)
+    assert child.returncode == 0 and "child done" in out, err[-2000:]
+    assert r0.overflowed_frames() == 0
+    for k in range(K):
+        assert np.array_equal(got[k][0], full[k][0]) and np.array_equal(got[k][1], full[k][1]), k
     r0.peer_frame_detach()
     r0.close()
 
