@@ -13,8 +13,8 @@ HEADERS = ["nrf_device.cuh", "nrf_snapshot.h", "../../include/nerf_b200.h", "../
            "../../include/nerf-cuda/nerf_render.h", "../host/render_server.cpp", "../host/testbed.cpp"]
 # host executables (C++ over the C ABI): the reference's render_server / testbed counterparts
 HOST_EXES = {"render_server": "host/render_server.cpp", "testbed": "host/testbed.cpp"}
-# -fmad=false: the march / encode / SH expression trees are the reference's, evaluated without FMA contraction so
-# they are bit-exact against the oracle (DESIGN.md numerics contract).  Nothing on the path is FMA-throughput bound.
+# -fmad=false: no contraction by the compiler; the FMAs the reference's nvcc build contracts are spelled __fmaf_rn in the
+# sources, so the march / encode / SH arithmetic is bit-exact against a run of the reference's CUDA build.
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
               "-Xcompiler", "-fPIC,-ffp-contract=off", "-Xptxas", "-v"]
 
@@ -34,6 +34,58 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
+def declared_symbols():
+    """Every function include/nerf_b200.h and include/nerf_b200_ext.h declare: the library's whole export list."""
+    import re
+    names = []
+    for h in ("nerf_b200.h", "nerf_b200_ext.h"):
+        src = open(os.path.join(HERE, "..", "include", h)).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        names += re.findall(r"\b(nrf_[a-z0-9_]+)\s*\(", src)
+    return sorted(set(names))
+
+
+def export_map() -> str:
+    """Linker version script: exactly the declared C ABI is visible; kernels' host stubs, cross-TU launch helpers and
+    experiment hooks stay local to the library."""
+    os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    path = os.path.join(HERE, "build", "exports.map")
+    with open(path, "w") as f:
+        f.write("{\n  global:\n" + "".join(f"    {n};\n" for n in declared_symbols()) + "  local: *;\n};\n")
+    return path
+
+
+# Experiment builds (A/B evidence for DESIGN.md §4, never the product): name -> extra -D flags for the kernel TUs.
+VARIANTS = {
+    "floor_magic": ["-DNRF_EXP_FLOOR_MAGIC=1"],        # floor/F2I (XU pipe) -> FADD.RZ magic constant (FMA pipe)
+    "evict": ["-DNRF_EXP_EVICT=1"],                    # table loads L2::evict_last, sample stream loads/stores evict_first
+    "smem_l01": ["-DNRF_EXP_SMEM_L01=1"],              # dense levels 0-1 staged in shared memory (LDS instead of LDG)
+    "floor_magic_evict": ["-DNRF_EXP_FLOOR_MAGIC=1", "-DNRF_EXP_EVICT=1"],
+}
+
+
+def build_variant(name: str) -> str:
+    """libnerf_b200_<name>.so next to the product library (load it with NRF_LIB=<path>)."""
+    out = os.path.join(HERE, f"libnerf_b200_{name}.so")
+    objs = []
+    os.makedirs(os.path.join(HERE, "build", name), exist_ok=True)
+    for s in SOURCES:
+        o = os.path.join(HERE, "build", name, s.replace(".cu", ".o"))
+        r = subprocess.run([_nvcc(), *NVCC_FLAGS, *VARIANTS[name], "-c", os.path.join(CSRC, s), "-o", o], capture_output=True, text=True)
+        if r.returncode != 0:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError(f"nvcc failed on {s} ({name})")
+        objs.append(o)
+        with open(os.path.join(HERE, "build", name, s.replace(".cu", ".ptxas.log")), "w") as f:
+            f.write(r.stderr)
+    r = subprocess.run([_nvcc(), "-shared", "-o", out, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-lcudart",
+                        "-Xlinker", f"--version-script={export_map()}"], capture_output=True, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("nvcc link failed")
+    return out
+
+
 def build(force=False, verbose=False) -> str:
     if not force and not needs_build():
         return LIB
@@ -49,7 +101,8 @@ def build(force=False, verbose=False) -> str:
             sys.stderr.write(r.stdout + r.stderr)
             raise RuntimeError(f"nvcc failed on {s}")
         objs.append(o)
-    cmd = [_nvcc(), "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"]
+    cmd = [_nvcc(), "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-lcudart",
+           "-Xlinker", f"--version-script={export_map()}"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
@@ -69,4 +122,8 @@ def build(force=False, verbose=False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--variant" in sys.argv:
+        for v in sys.argv[sys.argv.index("--variant") + 1].split(","):
+            print(build_variant(v))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -15,7 +15,8 @@ import numpy as np
 from .synthetic import ModelDesc
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libnerf_b200.so")
+# NRF_LIB: an experiment build of the same library (nerf_cuda_b200/build.py --variant), for A/B measurements only
+LIB_PATH = os.environ.get("NRF_LIB") or os.path.join(HERE, "libnerf_b200.so")
 
 
 class NerfError(RuntimeError):

@@ -37,6 +37,15 @@
 #define NET_GROUPS_DEFAULT 8   // tile groups (of 128 threads) per persistent CTA; 7 / 6 are experiment variants (NRF_NET_GROUPS)
 #define SMEM_W_BYTES 20480
 #define NET_SMEM (SMEM_W_BYTES + 128)
+#define NET_SMEM_L01 (66 * 1024)   // experiment NRF_EXP_SMEM_L01: room for the two coarsest (dense) levels behind the weights
+#ifdef NRF_EXP_SMEM_L01
+#if NRF_EXP_SMEM_L01
+#define NET_SMEM_LAUNCH (NET_SMEM + NET_SMEM_L01)
+#endif
+#endif
+#ifndef NET_SMEM_LAUNCH
+#define NET_SMEM_LAUNCH NET_SMEM
+#endif
 // byte offsets of the packed weight matrices inside the 20 KB block
 #define W0_OFF 0       // [64 x 32]
 #define W1_OFF 4096    // [16 x 64]
@@ -160,12 +169,67 @@ struct LevelTaps {
   float w0, w1, w2;
 };
 
+// ---- experiment hooks (nerf_cuda_b200/build.py VARIANTS; all off in the product build; results in DESIGN.md §4) ----
+#ifndef NRF_EXP_FLOOR_MAGIC
+#define NRF_EXP_FLOOR_MAGIC 0
+#endif
+#ifndef NRF_EXP_EVICT
+#define NRF_EXP_EVICT 0
+#endif
+#ifndef NRF_EXP_SMEM_L01
+#define NRF_EXP_SMEM_L01 0
+#endif
+#if NRF_EXP_EVICT
+// table entries: keep in L2 (evict_last); sample records / outputs: streamed once (evict_first, no L1 allocation)
+__device__ __forceinline__ uint64_t policy_evict_last() { uint64_t p; asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p)); return p; }
+__device__ __forceinline__ uint64_t policy_evict_first() { uint64_t p; asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p; }
+__device__ __forceinline__ uint32_t tab_ld32(const uint32_t* a) {
+  uint32_t v;
+  asm("ld.global.nc.L2::cache_hint.b32 %0, [%1], %2;" : "=r"(v) : "l"(a), "l"(policy_evict_last()));
+  return v;
+}
+__device__ __forceinline__ uint2 tab_ld64(const uint2* a) {
+  uint2 v;
+  asm("ld.global.nc.L2::cache_hint.v2.b32 {%0,%1}, [%2], %3;" : "=r"(v.x), "=r"(v.y) : "l"(a), "l"(policy_evict_last()));
+  return v;
+}
+__device__ __forceinline__ float4 sample_ld(const float4* a) {
+  float4 f;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=f"(f.x), "=f"(f.y), "=f"(f.z), "=f"(f.w) : "l"(a), "l"(policy_evict_first()));
+  return f;
+}
+__device__ __forceinline__ void out_st(uint2* a, uint2 v) {
+  asm volatile("st.global.L2::cache_hint.v2.b32 [%0], {%1,%2}, %3;" ::"l"(a), "r"(v.x), "r"(v.y), "l"(policy_evict_first()) : "memory");
+}
+#else
+__device__ __forceinline__ uint32_t tab_ld32(const uint32_t* a) { return __ldg(a); }
+__device__ __forceinline__ uint2 tab_ld64(const uint2* a) { return __ldg(a); }
+__device__ __forceinline__ float4 sample_ld(const float4* a) { return __ldg(a); }
+__device__ __forceinline__ void out_st(uint2* a, uint2 v) { *a = v; }
+#endif
+
+__device__ __forceinline__ uint32_t lds32(uint32_t saddr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(saddr));
+  return v;
+}
+// stab != 0 (experiment NRF_EXP_SMEM_L01): this DENSE level's table sits in shared memory at that address
 template <bool IDX>
-__device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float u1, float u2, LevelTaps& T, uint32_t* idx_out) {
+__device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float u1, float u2, LevelTaps& T, uint32_t* idx_out,
+                                           uint32_t stab = 0) {
   // pos_fract (common_device.h:424-431): input*scale + 0.5 is ONE FFMA in the reference's kernel_grid SASS
   const float p0 = __fmaf_rn(u0, lv.scale, 0.5f), p1 = __fmaf_rn(u1, lv.scale, 0.5f), p2 = __fmaf_rn(u2, lv.scale, 0.5f);
+#if NRF_EXP_FLOOR_MAGIC
+  // 0 <= p < 2^23: p + 2^23 rounded toward zero IS floor(p) + 2^23 (ulp 1 there) — FADD.RZ on the FMA pipe instead of
+  // FRND + F2I on the quarter-rate XU pipe; the integer is the low mantissa
+  const float m0 = __fadd_rz(p0, 8388608.f), m1 = __fadd_rz(p1, 8388608.f), m2 = __fadd_rz(p2, 8388608.f);
+  const float f0 = m0 - 8388608.f, f1 = m1 - 8388608.f, f2 = m2 - 8388608.f;
+  const uint32_t g0 = __float_as_uint(m0) & 0x7fffffu, g1 = __float_as_uint(m1) & 0x7fffffu, g2 = __float_as_uint(m2) & 0x7fffffu;
+#else
   const float f0 = floorf(p0), f1 = floorf(p1), f2 = floorf(p2);
   const uint32_t g0 = (uint32_t)(int)f0, g1 = (uint32_t)(int)f1, g2 = (uint32_t)(int)f2;
+#endif
   T.w0 = p0 - f0; T.w1 = p1 - f1; T.w2 = p2 - f2;
   const uint32_t* __restrict__ tl = lv.tab;
   uint32_t e[8];
@@ -182,9 +246,9 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const uint2 q = __ldg(reinterpret_cast<const uint2*>(tl) + (e[2 * j] >> 1));
+      const uint2 q = tab_ld64(reinterpret_cast<const uint2*>(tl) + (e[2 * j] >> 1));
       uint32_t far = 0;
-      if (odd) far = __ldg(tl + e[2 * j + 1]);
+      if (odd) far = tab_ld32(tl + e[2 * j + 1]);
       const bool up = e[2 * j] & 1u;
       T.raw[2 * j] = up ? q.y : q.x;
       T.raw[2 * j + 1] = odd ? far : (up ? q.x : q.y);
@@ -202,7 +266,7 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
       e[2 * j + 1] = (g0p ^ yz[j]) & m;
     }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) T.raw[k] = __ldg(tl + e[k]);
+    for (int k = 0; k < 8; ++k) T.raw[k] = tab_ld32(tl + e[k]);
   } else if (lv.hashed == 3) {
     // res^3 wrapped below T in the reference's 32-bit stride (grid.h:100-117): dense index, 32-bit wrap, mod T (a power of 2)
     const uint32_t r1 = lv.res, r2 = lv.res * lv.res, m = lv.size - 1u;
@@ -214,7 +278,7 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
       e[2 * j + 1] = (b + off[j] + 1u) & m;
     }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) T.raw[k] = __ldg(tl + e[k]);
+    for (int k = 0; k < 8; ++k) T.raw[k] = tab_ld32(tl + e[k]);
   } else {
     const uint32_t r1 = lv.res, r2 = lv.res * lv.res, Tl = lv.size;
     const uint32_t b = g0 + g1 * r1 + g2 * r2;
@@ -225,8 +289,13 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
       e[2 * j] = min(a, a - Tl);
       e[2 * j + 1] = min(c, c - Tl);
     }
+    if (NRF_EXP_SMEM_L01 && stab) {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) T.raw[k] = __ldg(tl + e[k]);
+      for (int k = 0; k < 8; ++k) T.raw[k] = lds32(stab + e[k] * 4u);
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) T.raw[k] = tab_ld32(tl + e[k]);
+    }
   }
   if (IDX && idx_out) {
 #pragma unroll
@@ -275,14 +344,16 @@ __device__ __forceinline__ void ld_relu_pack32(uint32_t taddr, uint32_t* packed)
 #define SL3 13
 #endif
 template <int L0, int L1, bool IDX>
-__device__ __forceinline__ void gather_slice(const NetParams& P, const float4& s, uint32_t* f, uint32_t* idx_out) {
+__device__ __forceinline__ void gather_slice(const NetParams& P, const float4& s, uint32_t* f, uint32_t* idx_out,
+                                             uint32_t stab0 = 0, uint32_t stab1 = 0) {
   // two levels' loads in flight before either blend: measured 0.7 % faster than level by level (ptxas already
   // overlaps most of it; 7 groups x 72 registers then spill 4 bytes)
 #pragma unroll
   for (int l = L0; l < L1; l += 2) {
     LevelTaps A, B;
-    level_load<IDX>(P.lv[l], s.x, s.y, s.z, A, IDX && idx_out ? idx_out + l * 8 : nullptr);
-    if (l + 1 < L1) level_load<IDX>(P.lv[l + 1], s.x, s.y, s.z, B, IDX && idx_out ? idx_out + (l + 1) * 8 : nullptr);
+    level_load<IDX>(P.lv[l], s.x, s.y, s.z, A, IDX && idx_out ? idx_out + l * 8 : nullptr, l == 0 ? stab0 : (l == 1 ? stab1 : 0u));
+    if (l + 1 < L1)
+      level_load<IDX>(P.lv[l + 1], s.x, s.y, s.z, B, IDX && idx_out ? idx_out + (l + 1) * 8 : nullptr, l + 1 == 1 ? stab1 : 0u);
     f[l] = level_blend(A);
     if (l + 1 < L1) f[l + 1] = level_blend(B);
   }
@@ -366,6 +437,13 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     // weights: 20 KB, already in UMMA core-matrix order -> straight copy
     const uint4* src = P.mlp_packed;
     for (int i = tid; i < SMEM_W_BYTES / 16; i += NET_GROUPS * 128) reinterpret_cast<uint4*>(sW)[i] = __ldg(src + i);
+#if NRF_EXP_SMEM_L01
+    if (MODE == 2 && P.lv[0].hashed == 0 && P.lv[1].hashed == 0 && (P.lv[0].size + P.lv[1].size) * 4u <= NET_SMEM_L01) {
+      uint32_t* st = reinterpret_cast<uint32_t*>(smem + NET_SMEM);
+      const uint32_t n01 = P.lv[0].size + P.lv[1].size;   // level 1 follows level 0 in the table as well
+      for (uint32_t i = tid; i < n01; i += NET_GROUPS * 128) st[i] = __ldg(P.lv[0].tab + i);
+    }
+#endif
     if (gt == 0) mbar_init(bar, 1);
     if (warp == 0) {
       asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)) : "memory");
@@ -388,14 +466,20 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
   do { if (gt == 0) { tc_fence_after(); issue_layer_ts<N_, K_, NFULL_>(t_d, t_a, w_addr + (OFF_), (N0_)); umma_commit(bar); } } while (0)
 #define MMA_WAIT() do { mbar_wait(bar, phase); phase ^= 1; tc_fence_after(); } while (0)
 
+#if NRF_EXP_SMEM_L01
+  const bool staged = MODE == 2 && P.lv[0].hashed == 0 && P.lv[1].hashed == 0 && (P.lv[0].size + P.lv[1].size) * 4u <= NET_SMEM_L01;
+  const uint32_t stab0 = staged ? smem_u32(smem + NET_SMEM) : 0u, stab1 = staged ? stab0 + P.lv[0].size * 4u : 0u;
+#else
+  const uint32_t stab0 = 0, stab1 = 0;
+#endif
   // features of the group's first tile (pipeline prologue)
   uint32_t fn[16];
   float4 sn = make_float4(0.f, 0.f, 0.f, 0.f);
   int tile = t0 + g;
   if (MODE == 2 && tile < t1) {
     const int i = tile * NRF_TILE + gt;
-    if (i < n) sn = __ldg(samples + i);
-    gather_slice<0, 8, false>(P, sn, fn, nullptr);
+    if (i < n) sn = sample_ld(samples + i);
+    gather_slice<0, 8, false>(P, sn, fn, nullptr, stab0, stab1);
     gather_slice<8, 16, false>(P, sn, fn, nullptr);
   }
 
@@ -414,13 +498,13 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     const bool has_next = MODE == 2 && tile + NET_GROUPS < t1;   // uniform over the group
     if (has_next) {
       const int in = i + NET_GROUPS * NRF_TILE;
-      sn = in < n ? __ldg(samples + in) : make_float4(0.f, 0.f, 0.f, 0.f);
+      sn = in < n ? sample_ld(samples + in) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     tmem_wait_st();
     // ---- density layer 0: 32 -> 64 (two N=32 halves), ReLU ---------------------------------------------------------
     GROUP_SYNC();
     ISSUE(32, 32, 64, W0_OFF, 0);
-    if (has_next) gather_slice<0, 4, false>(P, sn, fn, nullptr);
+    if (has_next) gather_slice<0, 4, false>(P, sn, fn, nullptr, stab0, stab1);
     uint32_t h[32];
     MMA_WAIT();
     ld_relu_pack32(t_d + lane_off, h);
@@ -505,7 +589,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
         const __half r = act_h(P.rgb_act, __float2half_rn(__uint_as_float(a[0])));
         const __half gg = act_h(P.rgb_act, __float2half_rn(__uint_as_float(a[1])));
         const __half b = act_h(P.rgb_act, __float2half_rn(__uint_as_float(a[2])));
-        out[i] = make_uint2(pack_h2(r, gg), pack_h2(b, sigma));
+        out_st(out + i, make_uint2(pack_h2(r, gg), pack_h2(b, sigma)));
       }
     }
     // the next tile's first tcgen05.st / MMA of this group must not overtake these TMEM reads
@@ -595,8 +679,8 @@ extern "C" __global__ void k_probe_sh(int n, const float4* __restrict__ dirs01, 
 template <int MODE, int G>
 static void net_attr() {
   // 20.6 KB of shared memory per SM; leave the rest of the unified array to L1 (carveout in percent of 228 KB)
-  cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NET_SMEM);
-  static const int carveout = getenv("NRF_NET_CARVEOUT") ? atoi(getenv("NRF_NET_CARVEOUT")) : 16;
+  cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NET_SMEM_LAUNCH);
+  static const int carveout = getenv("NRF_NET_CARVEOUT") ? atoi(getenv("NRF_NET_CARVEOUT")) : (NRF_EXP_SMEM_L01 ? 40 : 16);
   cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
 }
 static int g_net_groups = 7;   // measured on B200 (C3): 7 groups = 896 threads x 72 registers, no spills: 3-4 % faster than 8 x 64 (spills), 6 is slower again
@@ -622,12 +706,12 @@ extern "C" cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t strea
   if (n <= 0) return cudaSuccess;
 #define NET_ARGS *P, n, samples, sample_ray, rays, ray_sh, dirs_mode, enc_io, out, idx_out, n_dev, S
   switch (mode) {
-    case 0: k_network<0, 8><<<grid, 1024, NET_SMEM, stream>>>(NET_ARGS); break;
-    case 1: k_network<1, 8><<<grid, 1024, NET_SMEM, stream>>>(NET_ARGS); break;
+    case 0: k_network<0, 8><<<grid, 1024, NET_SMEM_LAUNCH, stream>>>(NET_ARGS); break;
+    case 1: k_network<1, 8><<<grid, 1024, NET_SMEM_LAUNCH, stream>>>(NET_ARGS); break;
     default:
-      if (g_net_groups == 7) k_network<2, 7><<<grid, 896, NET_SMEM, stream>>>(NET_ARGS);
-      else if (g_net_groups == 6) k_network<2, 6><<<grid, 768, NET_SMEM, stream>>>(NET_ARGS);
-      else k_network<2, 8><<<grid, 1024, NET_SMEM, stream>>>(NET_ARGS);
+      if (g_net_groups == 7) k_network<2, 7><<<grid, 896, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
+      else if (g_net_groups == 6) k_network<2, 6><<<grid, 768, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
+      else k_network<2, 8><<<grid, 1024, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
       break;
   }
 #undef NET_ARGS

@@ -449,6 +449,24 @@ static int upload_model(nrf_ctx* c, Device& D, const float* params, size_t n_par
   }
   N.mlp_rowmaj = D.params_h.p;
   N.table = reinterpret_cast<const __half2*>(D.params_h.p + 10240);
+  // experiment knob (A/B in DESIGN.md §4, off by default): NRF_L2_PERSIST=<MB> sets aside that much L2 for persisting lines
+  // and marks the hash table as the stream's persisting access window, everything else as streaming
+  if (const char* e = std::getenv("NRF_L2_PERSIST")) {
+    const size_t want = (size_t)std::atoi(e) << 20;
+    if (want > 0) {
+      cudaDeviceProp prop;
+      CU(cudaGetDeviceProperties(&prop, D.dev));
+      const size_t table_bytes = (size_t)c->levels.offsets[d.n_levels] * 4;
+      CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, std::min(want, (size_t)prop.persistingL2CacheMaxSize)));
+      cudaStreamAttrValue attr{};
+      attr.accessPolicyWindow.base_ptr = const_cast<__half*>(D.params_h.p + 10240);
+      attr.accessPolicyWindow.num_bytes = std::min(table_bytes, (size_t)prop.accessPolicyMaxWindowSize);
+      attr.accessPolicyWindow.hitRatio = std::min(1.0f, (float)std::min(want, (size_t)prop.persistingL2CacheMaxSize) / (float)table_bytes);
+      attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+      attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+      CU(cudaStreamSetAttribute(D.stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+    }
+  }
   for (uint32_t l = 0; l < d.n_levels; ++l) N.lv[l].tab = reinterpret_cast<const uint32_t*>(N.table) + N.lv[l].offset;
   N.mlp_packed = D.mlp_packed.p;
   N.rgb_act = d.rgb_activation;
@@ -1682,6 +1700,9 @@ extern "C" int nrf_peer_frame_collect(nrf_ctx* c, int back, uint8_t** rgb, uint8
   const int slot = (int)((c->peer_seq - (unsigned)back) & 1u);
   if (!c->peer_owned) { CU(cudaEventSynchronize(c->peer_done[slot])); return NRF_OK; }
   uint8_t* host = c->peer_host + (size_t)slot * c->W * c->H * 4;
+  // the latest frame must be a valid one first: a frame of this rank that did not fit its sample buffers is rendered again
+  // here (same slot, same sequence number; its fence and copy are enqueued again behind it)
+  if (back == 0) { int rc_ = frame_resolve(c); if (rc_) return rc_; }
   if (!c->peer_copy_out) {   // not copied behind the fence: do it now, after the slot's fence, on the copy stream
     if (back != 0) return fail(NRF_ESTATE, "nrf_peer_frame_collect: an earlier frame needs nrf_peer_frame_copy_out");
     CU(cudaMemcpyAsync(host, c->peer_frame + (size_t)slot * c->W * c->H * 4, (size_t)c->W * c->H * 4, cudaMemcpyDeviceToHost,
@@ -1690,7 +1711,6 @@ extern "C" int nrf_peer_frame_collect(nrf_ctx* c, int back, uint8_t** rgb, uint8
   } else {
     CU(cudaEventSynchronize(c->peer_copied[slot]));
   }
-  if (back == 0) { int rc_ = frame_resolve(c); if (rc_) return rc_; }   // the latest frame must also be a valid one
   if (rgb) *rgb = host;
   if (depth) *depth = host + (size_t)c->W * c->H * 3;
   return NRF_OK;

@@ -421,6 +421,7 @@ poses = [syn.look_at_pose(syn.camera_radius(name), 20.0, 45.0 * k) for k in rang
 for p in poses:                      # size the sample buffers before the peer frame counts frames
     r.render_frame_device(intr, p)
 r.synchronize()
+ovf0 = r.overflowed_frames()         # (the sizing pass above overflows by design: a fresh context starts at 32 samples per ray)
 r.peer_frame_attach(bytes.fromhex(sys.stdin.readline().strip()))
 for k, p in enumerate(poses):        # no host sync between frames: the ack flag is what holds this rank back
     r.render_frame_device(intr, p)
@@ -428,7 +429,7 @@ for k, p in enumerate(poses):        # no host sync between frames: the ack flag
         r.peer_frame_collect(1)
 r.peer_frame_collect(0)
 r.synchronize()
-assert r.overflowed_frames() == 0
+assert r.overflowed_frames() == ovf0
 r.peer_frame_detach()
 r.close()
 print("child done")
@@ -457,6 +458,7 @@ def test_peer_frame_one_sided_fence_pipeline(pair, tmp_path):
     for p in poses:
         r0.render_frame_device(intr, p)
     r0.synchronize()
+    ovf0 = r0.overflowed_frames()
     handle = r0.peer_frame_export()
     r0.peer_frame_copy_out(True)
     script = tmp_path / "peer_pipe_child.py"
@@ -475,7 +477,7 @@ def test_peer_frame_one_sided_fence_pipeline(pair, tmp_path):
     got.append(tuple(a.copy() for a in r0.peer_frame_collect(0)))
     out, err = child.communicate(timeout=300)
     assert child.returncode == 0 and "child done" in out, err[-2000:]
-    assert r0.overflowed_frames() == 0
+    assert r0.overflowed_frames() == ovf0
     for k in range(K):
         assert np.array_equal(got[k][0], full[k][0]) and np.array_equal(got[k][1], full[k][1]), k
     r0.peer_frame_detach()

@@ -33,6 +33,11 @@ def test_library_exports_every_declared_symbol(built_lib):
         assert hasattr(lib, s), f"{s} declared in include/*.h but not exported by libnerf_b200.so"
     assert set(capi.EXPORTS) <= set(syms)
     assert b"sm_100a" in lib.nrf_version()
+    # ... and nothing else: kernel stubs, cross-TU launch helpers and experiment hooks are local (linker version script)
+    import subprocess
+    out = subprocess.run(["nm", "-D", "--defined-only", built_lib], capture_output=True, text=True, check=True).stdout
+    exported = sorted(ln.split()[-1].split("@")[0] for ln in out.splitlines() if len(ln.split()) == 3 and ln.split()[1] in "TDBR")
+    assert exported == syms, sorted(set(exported) ^ set(syms))
 
 
 def test_no_cpu_fallback(built_lib):
