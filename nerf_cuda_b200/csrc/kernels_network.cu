@@ -215,9 +215,12 @@ __device__ __forceinline__ uint32_t lds32(uint32_t saddr) {
   return v;
 }
 // stab != 0 (experiment NRF_EXP_SMEM_L01): this DENSE level's table sits in shared memory at that address
-template <bool IDX>
+// LM >= 0: the level's addressing mode is known at compile time (kernel specialised for the model's level layout, see
+// NRF_LMODES_T19): no jump table per level and half the code; LM < 0: read from the level descriptor.
+template <bool IDX, int LM = -1>
 __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float u1, float u2, LevelTaps& T, uint32_t* idx_out,
                                            uint32_t stab = 0) {
+  const uint32_t mode = LM >= 0 ? (uint32_t)LM : lv.hashed;
   // pos_fract (common_device.h:424-431): input*scale + 0.5 is ONE FFMA in the reference's kernel_grid SASS
   const float p0 = __fmaf_rn(u0, lv.scale, 0.5f), p1 = __fmaf_rn(u1, lv.scale, 0.5f), p2 = __fmaf_rn(u2, lv.scale, 0.5f);
 #if NRF_EXP_FLOOR_MAGIC
@@ -233,7 +236,7 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
   T.w0 = p0 - f0; T.w1 = p1 - f1; T.w2 = p2 - f2;
   const uint32_t* __restrict__ tl = lv.tab;
   uint32_t e[8];
-  if (lv.hashed == 1) {
+  if (mode == 1) {
     const uint32_t m = lv.size - 1u;
     const uint32_t hy0 = g1 * 2654435761u, hy1 = hy0 + 2654435761u, hz0 = g2 * 805459861u, hz1 = hz0 + 805459861u;
     const uint32_t yz[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
@@ -253,7 +256,7 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
       T.raw[2 * j] = up ? q.y : q.x;
       T.raw[2 * j + 1] = odd ? far : (up ? q.x : q.y);
     }
-  } else if (lv.hashed == 2) {
+  } else if (mode == 2) {
     // hashed level, plain 4-byte loads (no slot pairing): fewer instructions, more L1 wavefronts — chosen per level on
     // the host for the levels whose lanes share cache lines anyway (NRF_PAIR_FROM)
     const uint32_t m = lv.size - 1u;
@@ -267,7 +270,7 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) T.raw[k] = tab_ld32(tl + e[k]);
-  } else if (lv.hashed == 3) {
+  } else if (mode == 3) {
     // res^3 wrapped below T in the reference's 32-bit stride (grid.h:100-117): dense index, 32-bit wrap, mod T (a power of 2)
     const uint32_t r1 = lv.res, r2 = lv.res * lv.res, m = lv.size - 1u;
     const uint32_t b = g0 + g1 * r1 + g2 * r2;
@@ -343,20 +346,31 @@ __device__ __forceinline__ void ld_relu_pack32(uint32_t taddr, uint32_t* packed)
 #define SL2 10
 #define SL3 13
 #endif
-template <int L0, int L1, bool IDX>
-__device__ __forceinline__ void gather_slice(const NetParams& P, const float4& s, uint32_t* f, uint32_t* idx_out,
-                                             uint32_t stab0 = 0, uint32_t stab1 = 0) {
+#define NRF_LMODES_RUNTIME 0xFFFFFFFFu
+// 2 bits per level: the layout of every log2_hashmap_size = 19 model with the base.json grid (C2, C3, C4): levels 0-4 dense,
+// 5-11 hashed with 4-byte loads, 12-15 hashed with slot-paired loads (NRF_PAIR_FROM = 12)
+#define NRF_LMODES_T19 0x55AAA800u
+template <int L, int L1, bool IDX, uint32_t LMODES>
+__device__ __forceinline__ void gather_pairs(const NetParams& P, const float4& s, uint32_t* f, uint32_t* idx_out, uint32_t stab0,
+                                             uint32_t stab1) {
   // two levels' loads in flight before either blend: measured 0.7 % faster than level by level (ptxas already
   // overlaps most of it; 7 groups x 72 registers then spill 4 bytes)
-#pragma unroll
-  for (int l = L0; l < L1; l += 2) {
+  if constexpr (L < L1) {
+    constexpr int M0 = LMODES == NRF_LMODES_RUNTIME ? -1 : (int)((LMODES >> (2 * L)) & 3u);
+    constexpr int M1 = LMODES == NRF_LMODES_RUNTIME ? -1 : (int)((LMODES >> (2 * ((L + 1) & 15))) & 3u);
     LevelTaps A, B;
-    level_load<IDX>(P.lv[l], s.x, s.y, s.z, A, IDX && idx_out ? idx_out + l * 8 : nullptr, l == 0 ? stab0 : (l == 1 ? stab1 : 0u));
-    if (l + 1 < L1)
-      level_load<IDX>(P.lv[l + 1], s.x, s.y, s.z, B, IDX && idx_out ? idx_out + (l + 1) * 8 : nullptr, l + 1 == 1 ? stab1 : 0u);
-    f[l] = level_blend(A);
-    if (l + 1 < L1) f[l + 1] = level_blend(B);
+    level_load<IDX, M0>(P.lv[L], s.x, s.y, s.z, A, IDX && idx_out ? idx_out + L * 8 : nullptr, L == 0 ? stab0 : (L == 1 ? stab1 : 0u));
+    if constexpr (L + 1 < L1)
+      level_load<IDX, M1>(P.lv[L + 1], s.x, s.y, s.z, B, IDX && idx_out ? idx_out + (L + 1) * 8 : nullptr, L + 1 == 1 ? stab1 : 0u);
+    f[L] = level_blend(A);
+    if constexpr (L + 1 < L1) f[L + 1] = level_blend(B);
+    gather_pairs<L + 2, L1, IDX, LMODES>(P, s, f, idx_out, stab0, stab1);
   }
+}
+template <int L0, int L1, bool IDX, uint32_t LMODES = NRF_LMODES_RUNTIME>
+__device__ __forceinline__ void gather_slice(const NetParams& P, const float4& s, uint32_t* f, uint32_t* idx_out,
+                                             uint32_t stab0 = 0, uint32_t stab1 = 0) {
+  gather_pairs<L0, L1, IDX, LMODES>(P, s, f, idx_out, stab0, stab1);
 }
 
 // Occupancy experiment (not on the frame path): encode-only with THREADS per CTA and MINB CTAs per SM.
@@ -390,7 +404,7 @@ extern "C" cudaError_t nrf_launch_encode_exp(int variant, int sms, cudaStream_t 
   return cudaGetLastError();
 }
 
-template <int MODE, int NET_GROUPS = NET_GROUPS_DEFAULT>
+template <int MODE, int NET_GROUPS = NET_GROUPS_DEFAULT, uint32_t LMODES = NRF_LMODES_RUNTIME>
 __global__ void __launch_bounds__(NET_GROUPS * 128, 1)
 k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__ samples,
           const int* __restrict__ sample_ray, const float4* __restrict__ rays, const uint4* __restrict__ ray_sh,
@@ -479,8 +493,8 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
   if (MODE == 2 && tile < t1) {
     const int i = tile * NRF_TILE + gt;
     if (i < n) sn = sample_ld(samples + i);
-    gather_slice<0, 8, false>(P, sn, fn, nullptr, stab0, stab1);
-    gather_slice<8, 16, false>(P, sn, fn, nullptr);
+    gather_slice<0, 8, false, LMODES>(P, sn, fn, nullptr, stab0, stab1);
+    gather_slice<8, 16, false, LMODES>(P, sn, fn, nullptr);
   }
 
   for (; tile < t1; tile += NET_GROUPS) {
@@ -504,7 +518,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     // ---- density layer 0: 32 -> 64 (two N=32 halves), ReLU ---------------------------------------------------------
     GROUP_SYNC();
     ISSUE(32, 32, 64, W0_OFF, 0);
-    if (has_next) gather_slice<0, 4, false>(P, sn, fn, nullptr, stab0, stab1);
+    if (has_next) gather_slice<0, 4, false, LMODES>(P, sn, fn, nullptr, stab0, stab1);
     uint32_t h[32];
     MMA_WAIT();
     ld_relu_pack32(t_d + lane_off, h);
@@ -518,7 +532,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     tmem_wait_st();
     GROUP_SYNC();
     ISSUE(16, 64, 16, W1_OFF, 0);
-    if (has_next) gather_slice<4, SL1, false>(P, sn, fn, nullptr);
+    if (has_next) gather_slice<4, SL1, false, LMODES>(P, sn, fn, nullptr);
     // SH coefficients of the direction (per ray)
     uint32_t sh[8];
     if (dirs_mode == 0) {
@@ -553,7 +567,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     tmem_wait_st();
     GROUP_SYNC();
     ISSUE(32, 32, 64, V0_OFF, 0);
-    if (has_next) gather_slice<SL1, SL2, false>(P, sn, fn, nullptr);
+    if (has_next) gather_slice<SL1, SL2, false, LMODES>(P, sn, fn, nullptr);
     MMA_WAIT();
     ld_relu_pack32(t_d + lane_off, h);
     GROUP_SYNC();
@@ -566,7 +580,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     tmem_wait_st();
     GROUP_SYNC();
     ISSUE(32, 64, 64, V1_OFF, 0);
-    if (has_next) gather_slice<SL2, SL3, false>(P, sn, fn, nullptr);
+    if (has_next) gather_slice<SL2, SL3, false, LMODES>(P, sn, fn, nullptr);
     MMA_WAIT();
     ld_relu_pack32(t_d + lane_off, h);
     GROUP_SYNC();
@@ -579,7 +593,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     tmem_wait_st();
     GROUP_SYNC();
     ISSUE(16, 64, 16, V2_OFF, 0);
-    if (has_next) gather_slice<SL3, 16, false>(P, sn, fn, nullptr);
+    if (has_next) gather_slice<SL3, 16, false, LMODES>(P, sn, fn, nullptr);
     MMA_WAIT();
     {
       uint32_t a[16];
@@ -676,18 +690,20 @@ extern "C" __global__ void k_probe_sh(int n, const float4* __restrict__ dirs01, 
 }
 
 // ------------------------------------------------------------------------------------------------ host launchers
-template <int MODE, int G>
+template <int MODE, int G, uint32_t LM = NRF_LMODES_RUNTIME>
 static void net_attr() {
   // 20.6 KB of shared memory per SM; leave the rest of the unified array to L1 (carveout in percent of 228 KB)
-  cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NET_SMEM_LAUNCH);
+  cudaFuncSetAttribute(k_network<MODE, G, LM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NET_SMEM_LAUNCH);
   static const int carveout = getenv("NRF_NET_CARVEOUT") ? atoi(getenv("NRF_NET_CARVEOUT")) : (NRF_EXP_SMEM_L01 ? 40 : 16);
-  cudaFuncSetAttribute(k_network<MODE, G>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+  cudaFuncSetAttribute(k_network<MODE, G, LM>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
 }
+static bool g_specialise = true;   // NRF_NO_SPECIALISE=1: always the generic kernel (A/B, tests of the generic path at full size)
 static int g_net_groups = 7;   // measured on B200 (C3): 7 groups = 896 threads x 72 registers, no spills: 3-4 % faster than 8 x 64 (spills), 6 is slower again
 static void nrf_network_setup() {
   static bool attr_set = false;
   if (attr_set) return;
-  net_attr<0, 8>(); net_attr<1, 8>(); net_attr<2, 8>(); net_attr<2, 7>(); net_attr<2, 6>();
+  net_attr<0, 8>(); net_attr<1, 8>(); net_attr<2, 8>(); net_attr<2, 7>(); net_attr<2, 6>(); net_attr<2, 7, NRF_LMODES_T19>();
+  g_specialise = getenv("NRF_NO_SPECIALISE") == nullptr;
   if (const char* e = getenv("NRF_NET_GROUPS")) {   // experiment: fewer groups = more registers per thread
     const int g = atoi(e);
     if (g == 6 || g == 7 || g == 8) g_net_groups = g;
@@ -709,7 +725,14 @@ extern "C" cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t strea
     case 0: k_network<0, 8><<<grid, 1024, NET_SMEM_LAUNCH, stream>>>(NET_ARGS); break;
     case 1: k_network<1, 8><<<grid, 1024, NET_SMEM_LAUNCH, stream>>>(NET_ARGS); break;
     default:
-      if (g_net_groups == 7) k_network<2, 7><<<grid, 896, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
+      if (g_net_groups == 7) {
+        // the level layout of this model as 2 bits per level; the layout of the T = 2^19 models has its own instantiation
+        // (measured: C2 network 5.11 -> 4.88 ms, C3 unchanged; half the code: 4 992 instead of 9 384 SASS instructions)
+        uint32_t lm = 0;
+        for (int l = 0; l < NRF_L; ++l) lm |= (P->lv[l].hashed & 3u) << (2 * l);
+        if (g_specialise && lm == NRF_LMODES_T19) k_network<2, 7, NRF_LMODES_T19><<<grid, 896, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
+        else k_network<2, 7><<<grid, 896, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
+      }
       else if (g_net_groups == 6) k_network<2, 6><<<grid, 768, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
       else k_network<2, 8><<<grid, 1024, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
       break;
