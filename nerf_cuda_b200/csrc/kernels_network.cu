@@ -22,7 +22,7 @@
 //     that A (<= 32 columns) and D (32 columns) fit the group's 64 columns;
 //   * groups synchronise with their own named barrier and their own mbarrier, never with the whole CTA: while one
 //     group waits for an MMA the other 28 warps keep the gather's loads in flight.
-// The 8 groups of a CTA walk ONE contiguous chunk of tiles interleaved (tile = chunk + 8*j + g): at any time an SM works
+// The G groups of a CTA (7 on the frame path) walk ONE contiguous chunk of tiles interleaved (tile = chunk + G*j + g): at any time an SM works
 // on neighbouring patches / steps of the warp-interleaved sample list, which is what the L1 hit rate lives on.
 //
 // Numerics: hash indices and fp16 interpolation are bit-exact against the reference's CUDA build executed on a B200
@@ -34,7 +34,7 @@
 
 #include "nrf_device.cuh"
 
-#define NET_GROUPS_DEFAULT 8   // tile groups (of 128 threads) per persistent CTA; 7 / 6 are experiment variants (NRF_NET_GROUPS)
+#define NET_GROUPS_DEFAULT 8   // template default (stage probes MODE 0/1 run 8 groups x 128 threads); the frame path launches 7 (g_net_groups), 6 / 8 via NRF_NET_GROUPS
 #define SMEM_W_BYTES 20480
 #define NET_SMEM (SMEM_W_BYTES + 128)
 #define NET_SMEM_L01 (66 * 1024)   // experiment NRF_EXP_SMEM_L01: room for the two coarsest (dense) levels behind the weights
@@ -337,7 +337,7 @@ __device__ __forceinline__ void ld_relu_pack32(uint32_t taddr, uint32_t* packed)
 // dirs_mode 1: direction input already normalised, rays[i].xyz; SH evaluated here (stage probes)
 //
 // MODE 2 is software-pipelined inside every group: while the tensor core works on a layer of tile j, the group's
-// threads gather 3-4 levels of tile j+8 (the group's next tile).  The gather slices sit in the five MMA waits where no
+// threads gather 3-4 levels of tile j+G (the group's next tile, G = groups per CTA).  The gather slices sit in the five MMA waits where no
 // activation registers are live (after L0-lo, L1, V0-lo, V1-lo, V2 were issued), so the MLP's round-trip latency is
 // hidden behind the group's own gather instead of idling 4 of the SM's 32 warps.
 // level boundaries of the gather slices hidden in the five MMA waits of a tile: 0-4 | 4-SL1 | SL1-SL2 | SL2-SL3 | SL3-16
@@ -425,7 +425,7 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
 
   const int tid = threadIdx.x, warp = tid >> 5, g = tid >> 7, gt = tid & 127;
   const int n_tiles = (n + NRF_TILE - 1) / NRF_TILE;
-  // contiguous chunk of tiles per CTA, interleaved over its 8 groups
+  // contiguous chunk of tiles per CTA, interleaved over its NET_GROUPS groups
   const int per_cta = (n_tiles + gridDim.x - 1) / gridDim.x;
   const int t0 = blockIdx.x * per_cta, t1 = min(n_tiles, t0 + per_cta);
 

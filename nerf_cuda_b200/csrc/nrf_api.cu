@@ -726,7 +726,7 @@ static void set_pose(nrf_ctx* c, MarchParams& M, const float intr[4], const floa
   std::memcpy(M.intr, intr, 16);
 }
 
-// k_network is persistent: one 1024-thread CTA per SM (8 tile groups), fewer when there are fewer than 8 tiles per SM.
+// k_network is persistent: one 896-thread CTA per SM (7 tile groups of 128 threads), fewer CTAs when there are fewer than 8 tiles per SM.
 static int network_grid(nrf_ctx*, const Device& D, int n_samples) {
   const int tiles = (n_samples + NRF_TILE - 1) / NRF_TILE;
   return std::max(1, std::min(D.n_sms, (tiles + 7) / 8));
