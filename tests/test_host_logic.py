@@ -208,3 +208,28 @@ def test_snapshot_reader_errors_match_reference(built_lib, tmp_path):
     with pytest.raises(NerfError) as e:
         _inspect(p)
     assert e.value.code == -5
+
+
+def test_bench_reference_arm_contract_on_cpu():
+    """bench.py --impl reference: under torchrun only rank 0 works (the other ranks exit 0 silently); without the reference's
+    CUDA binary or a GPU the arm is the CPU port, and its JSON line carries the keys the driver reads."""
+    import json
+    import subprocess
+    import sys
+    bench = os.path.join(ROOT, "bench.py")
+    env = dict(os.environ, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1")
+    r = subprocess.run([sys.executable, bench, "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0 and r.stdout.strip() == ""
+    import torch
+    if torch.cuda.is_available():
+        return
+    env["RANK"] = "0"
+    env["LOCAL_RANK"] = "0"
+    r = subprocess.run([sys.executable, bench, "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0", "--workload", "C1"],
+                       capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stderr[-1000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "rays/s" and line["value"] > 0 and line["n_gpus"] == 2
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["d2h_bytes_per_step"] == 0
