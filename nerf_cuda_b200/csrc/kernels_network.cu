@@ -347,9 +347,13 @@ __device__ __forceinline__ void ld_relu_pack32(uint32_t taddr, uint32_t* packed)
 #define SL3 13
 #endif
 #define NRF_LMODES_RUNTIME 0xFFFFFFFFu
-// 2 bits per level: the layout of every log2_hashmap_size = 19 model with the base.json grid (C2, C3, C4): levels 0-4 dense,
-// 5-11 hashed with 4-byte loads, 12-15 hashed with slot-paired loads (NRF_PAIR_FROM = 12)
+// 2 bits per level: the layouts of the log2_hashmap_size = 19 models with the base.json grid.  aabb_scale 1 (C2): levels 0-4
+// dense, 5-11 hashed with 4-byte loads, 12-15 hashed with slot-paired loads (NRF_PAIR_FROM = 12); aabb_scale 16 (C3, C4: finer
+// per_level_scale): levels 0-3 dense, 4-11 hashed, 12-15 slot-paired
 #define NRF_LMODES_T19 0x55AAA800u
+#define NRF_LMODES_T19_B16 0x55AAAA00u
+// log2_hashmap_size = 24, aabb_scale 1 (C5): levels 0-8 dense, 9-11 hashed, 12-14 slot-paired, 15 the wrapped dense index
+#define NRF_LMODES_T24 0xD5A80000u
 template <int L, int L1, bool IDX, uint32_t LMODES>
 __device__ __forceinline__ void gather_pairs(const NetParams& P, const float4& s, uint32_t* f, uint32_t* idx_out, uint32_t stab0,
                                              uint32_t stab1) {
@@ -702,7 +706,7 @@ static int g_net_groups = 7;   // measured on B200 (C3): 7 groups = 896 threads 
 static void nrf_network_setup() {
   static bool attr_set = false;
   if (attr_set) return;
-  net_attr<0, 8>(); net_attr<1, 8>(); net_attr<2, 8>(); net_attr<2, 7>(); net_attr<2, 6>(); net_attr<2, 7, NRF_LMODES_T19>();
+  net_attr<0, 8>(); net_attr<1, 8>(); net_attr<2, 8>(); net_attr<2, 7>(); net_attr<2, 6>(); net_attr<2, 7, NRF_LMODES_T19>(); net_attr<2, 7, NRF_LMODES_T19_B16>(); net_attr<2, 7, NRF_LMODES_T24>();
   g_specialise = getenv("NRF_NO_SPECIALISE") == nullptr;
   if (const char* e = getenv("NRF_NET_GROUPS")) {   // experiment: fewer groups = more registers per thread
     const int g = atoi(e);
@@ -727,10 +731,12 @@ extern "C" cudaError_t nrf_launch_network(int mode, int grid, cudaStream_t strea
     default:
       if (g_net_groups == 7) {
         // the level layout of this model as 2 bits per level; the layout of the T = 2^19 models has its own instantiation
-        // (measured: C2 network 5.11 -> 4.88 ms, C3 unchanged; half the code: 4 992 instead of 9 384 SASS instructions)
+        // (measured: network C2 5.11 -> 4.88 ms, C3 8.97 -> 8.61, C4 23.8 -> 22.9; half the code: 4 992 instead of 9 384 SASS instructions)
         uint32_t lm = 0;
         for (int l = 0; l < NRF_L; ++l) lm |= (P->lv[l].hashed & 3u) << (2 * l);
         if (g_specialise && lm == NRF_LMODES_T19) k_network<2, 7, NRF_LMODES_T19><<<grid, 896, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
+        else if (g_specialise && lm == NRF_LMODES_T19_B16) k_network<2, 7, NRF_LMODES_T19_B16><<<grid, 896, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
+        else if (g_specialise && lm == NRF_LMODES_T24) k_network<2, 7, NRF_LMODES_T24><<<grid, 896, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
         else k_network<2, 7><<<grid, 896, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
       }
       else if (g_net_groups == 6) k_network<2, 6><<<grid, 768, NET_SMEM_LAUNCH, stream>>>(NET_ARGS);
