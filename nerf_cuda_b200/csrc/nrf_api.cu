@@ -969,6 +969,10 @@ static int render_common(nrf_ctx* c, const float intr[4], const float* pose, boo
   if (!c || !intr || !pose) return fail(NRF_EINVAL, "render: null argument");
   if (!c->loaded) return fail(NRF_ESTATE, "render_frame before reload_network_from_file");
   if (!c->W) return fail(NRF_ESTATE, "render_frame before set_resolution");
+  // with a peer frame attached the pixels go to the owner's buffer, not to this context's frame: the host copy of the
+  // synchronous call would return stale bytes
+  if (to_host && c->peer_frame)
+    return fail(NRF_ESTATE, "a peer frame is attached: render with nrf_render_frame_device and read the frame with nrf_peer_frame_collect");
   // No host sync here: an earlier asynchronous frame that is still unvalidated is superseded (its buffers are reused
   // in stream order; its total stays in the ring as a growth hint for the next sync point).
   int rc;
@@ -1005,6 +1009,7 @@ extern "C" int nrf_render_batch_rgbd(nrf_ctx* c, const float intr[4], const floa
   int rc = nrf_local_rays(c, &n_local);
   if (rc) return rc;
   if (!c->loaded) return fail(NRF_ESTATE, "render_batch before reload_network_from_file");
+  if (c->peer_frame) return fail(NRF_ESTATE, "nrf_render_batch: detach the peer frame first (its pixels live in the owner's buffer)");
   const size_t px = c->n_shards == 1 ? (size_t)c->W * c->H : (size_t)n_local;
   const size_t frame_bytes = px * 3, stage_bytes = px * (depth_out ? 4 : 3);
   if (n_poses == 0) return NRF_OK;

@@ -2,6 +2,8 @@
 24: every fine level hashed into a 16 M-entry window, 1 GB table in HBM — tcnn grid.h:100-117 grid_index, :899-931 offset table),
 tcnn's initial table range U(-1e-4, 1e-4), C2 and C4 at full size.  The oracle renders bands of full pixel rows (seconds on the
 CPU); the rest of each frame is covered by the size-independent properties of test_full_size_c3_frame."""
+import os
+
 import numpy as np
 import pytest
 
@@ -97,3 +99,37 @@ def test_full_size_c2_and_c4_frames(built_lib, wl, pi, rows):
     u8, cnt = check_bands(r, O, syn.intrinsics(W, H), bench.poses_for(wl)[pi], W, H, rows, n_rows=1 if wl == "C4" else 2)
     assert (cnt > 0).mean() > 0.2
     r.close()
+
+
+def test_snapshot_written_by_the_reference_library_renders_like_its_arrays(built_lib):
+    """tests/golden/ref_nlohmann.msgpack (bytes produced by the reference's vendored nlohmann::json::to_msgpack: float64 and
+    integer-typed numbers, uint16/int16 encodings, alphabetical keys; 2 cascades, 32^3 grid, Sigmoid rgb, T = 2^8) loaded
+    through reload_network_from_file renders the same bytes as the same arrays handed over with load_raw, and the frame
+    agrees with the oracle built from those arrays (counts bit-exact)."""
+    from test_snapshot_fixtures import GOLD, expected_arrays, inspect   # (tests/ is on sys.path: rootdir conftest)
+    path = os.path.join(GOLD, "ref_nlohmann.msgpack")
+    desc, n_p, n_g, aabb, _, _ = inspect(path)
+    params, grid = expected_arrays()
+    assert n_p == params.size and n_g == grid.size
+    W, H = 80, 60
+    intr, pose = syn.intrinsics(W, H), syn.look_at_pose(6.0, 25.0, 40.0)
+    os.environ["NRF_SNAPSHOT_CACHE"] = "0"
+    try:
+        a = NerfRender(1)
+        a.reload_network_from_file(path)
+    finally:
+        os.environ.pop("NRF_SNAPSHOT_CACHE", None)
+    a.set_resolution((W, H))
+    rgb_a, dep_a = (x.copy() for x in a.render_frame(intr, pose))
+    fa, da, ca = (x.copy() for x in a.float_frame())
+    a.close()
+    b = NerfRender(1)
+    b.load_raw(desc, params, grid, aabb.astype(np.float32))
+    b.set_resolution((W, H))
+    rgb_b, dep_b = (x.copy() for x in b.render_frame(intr, pose))
+    O = orc.cuda_oracle(b, desc, params, grid, aabb.astype(np.float32))
+    b.close()
+    assert np.array_equal(rgb_a, rgb_b) and np.array_equal(dep_a, dep_b)
+    rgb_o, dep_o, cnt_o = O.render(intr, pose, W, H)
+    assert np.array_equal(ca, cnt_o) and ca.sum() > 0
+    assert np.abs(fa - rgb_o).max() <= IMG_TOL and np.abs(da - dep_o).max() <= 1e-3

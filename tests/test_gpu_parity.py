@@ -428,6 +428,10 @@ def test_peer_frame_ipc_two_processes(pair, tmp_path):
     assert np.array_equal(rgb, full_rgb) and np.array_equal(dep, full_dep)
     with pytest.raises(Exception):
         r0.set_resolution((W + 1, H))           # must detach first
+    with pytest.raises(Exception):
+        r0.render_frame(intr, pose)             # the host copy of the synchronous call would miss the peer buffer
+    with pytest.raises(Exception):
+        r0.render_batch(intr, np.stack([pose, pose]))
     r0.peer_frame_detach()
     r0.close()
 
