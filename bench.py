@@ -4,7 +4,8 @@
 A step = one frame = one pass of the hot path over W*H rays of the workload:
   default workload C3: 1920x1080, aabb_scale 16 (5 cascades), T=2^19, random-init weights, synthetic occupancy.
   N>1 (torchrun, one process per GPU): every rank renders its interleaved pixel blocks of the SAME frame
-  (strong scaling); the u8 framebuffer is gathered to rank 0 over NCCL/NVLink.
+  (strong scaling); every rank's composite kernel stores its u8 pixels into rank 0's frame over NVLink (CUDA IPC peer stores,
+  one-sided sequence-flag fence, no collective; --gather nccl = round 1's gather of packed tiles).
 
 JSON line (rank 0): value = rays/s with everything device-resident (the only host traffic inside a frame is the
 8-byte sample-count read-back the algorithm itself needs); e2e = same metric through the reference-facing call

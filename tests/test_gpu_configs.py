@@ -133,3 +133,27 @@ def test_snapshot_written_by_the_reference_library_renders_like_its_arrays(built
     rgb_o, dep_o, cnt_o = O.render(intr, pose, W, H)
     assert np.array_equal(ca, cnt_o) and ca.sum() > 0
     assert np.abs(fa - rgb_o).max() <= IMG_TOL and np.abs(da - dep_o).max() <= 1e-3
+
+
+def test_c1_whole_frame_against_the_oracle(built_lib):
+    """C1 (BASELINE.json configs[0], the CPU-runnable case: 200x200, C2's model, SURVEY.md §8d pose): the WHOLE frame against
+    the oracle — every ray's composited count bit-exact, every pixel within the image bars, the u8 frame within 2 LSB of the
+    cast of the oracle's floats (truncation at a .0 boundary may flip one LSB, never more)."""
+    import bench
+    cfg, W, H, _ = bench.WORKLOADS["C1"]
+    sc = syn.make_scene(cfg)
+    r = NerfRender(1)
+    r.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    r.set_resolution((W, H))
+    intr, pose = syn.intrinsics(W, H), bench.poses_for("C1")[0]
+    u8, d8 = (x.copy() for x in r.render_frame(intr, pose))
+    rgb, dep, cnt = (x.copy() for x in r.float_frame())
+    st = r.stats()
+    O = orc.cuda_oracle(r, sc.desc, sc.params, sc.grid, sc.aabb)
+    rgb2, dep2, cnt2 = O.render(intr, pose, W, H)
+    assert np.array_equal(cnt, cnt2) and st.n_samples_used == int(cnt2.sum()) > 0
+    assert np.abs(rgb - rgb2).max() <= IMG_TOL and np.abs(dep - dep2).max() <= 1e-3
+    mse = float(np.mean((np.clip(rgb, 0, 1).astype(np.float64) - np.clip(rgb2, 0, 1)) ** 2))
+    assert mse == 0 or 10 * np.log10(1.0 / mse) >= 45.0
+    assert np.abs(u8.astype(int) - O.to_u8(rgb2).reshape(H, W, 3).astype(int)).max() <= 2
+    r.close()
