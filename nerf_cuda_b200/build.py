@@ -61,6 +61,7 @@ VARIANTS = {
     "evict": ["-DNRF_EXP_EVICT=1"],                    # table loads L2::evict_last, sample stream loads/stores evict_first
     "smem_l01": ["-DNRF_EXP_SMEM_L01=1"],              # dense levels 0-1 staged in shared memory (LDS instead of LDG)
     "floor_magic_evict": ["-DNRF_EXP_FLOOR_MAGIC=1", "-DNRF_EXP_EVICT=1"],
+    "march_magic": ["-DNRF_EXP_MARCH_MAGIC=1"],      # march step: F2I.TRUNC x3 (XU pipe) -> FADD.RZ + mantissa mask
 }
 
 

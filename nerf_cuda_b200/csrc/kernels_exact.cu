@@ -18,6 +18,9 @@
 // position arithmetic, see k_emit).
 #include "nrf_device.cuh"
 
+#ifndef NRF_EXP_MARCH_MAGIC
+#define NRF_EXP_MARCH_MAGIC 0
+#endif
 #define RAYS_BLOCK 128
 #define RAYS_MIN_BLOCKS 8
 #define EMIT_CHUNK 8
@@ -159,9 +162,17 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
   const float halfH = R.halfH, hm1 = R.hm1;
   int nx, ny, nz;
   if (FAST) {
+#if NRF_EXP_MARCH_MAGIC
+    // experiment: the three F2I.TRUNC (quarter-rate XU pipe) as FADD.RZ with 2^23 — the operands lie in [0, H-1], so the
+    // truncated integer is the low mantissa of the sum
+    nx = (int)(__float_as_uint(__fadd_rz(fminf(__fmaf_rn(x, mip_rbound, 1.0f) * halfH, hm1), 8388608.f)) & 0x7fffffu);
+    ny = (int)(__float_as_uint(__fadd_rz(fminf(__fmaf_rn(y, mip_rbound, 1.0f) * halfH, hm1), 8388608.f)) & 0x7fffffu);
+    nz = (int)(__float_as_uint(__fadd_rz(fminf(__fmaf_rn(z, mip_rbound, 1.0f) * halfH, hm1), 8388608.f)) & 0x7fffffu);
+#else
     nx = (int)fminf(__fmaf_rn(x, mip_rbound, 1.0f) * halfH, hm1);
     ny = (int)fminf(__fmaf_rn(y, mip_rbound, 1.0f) * halfH, hm1);
     nz = (int)fminf(__fmaf_rn(z, mip_rbound, 1.0f) * halfH, hm1);
+#endif
   } else {
     nx = (int)clampf(__fmaf_rn(x, mip_rbound, 1.0f) * halfH, 0.0f, hm1);   // reference SASS: FFMA(x, rb, 1), DMUL x2
     ny = (int)clampf(__fmaf_rn(y, mip_rbound, 1.0f) * halfH, 0.0f, hm1);
