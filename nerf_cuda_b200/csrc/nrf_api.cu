@@ -988,10 +988,12 @@ static void start_workers(nrf_ctx* c) {
 }
 
 static int frame_enqueue_all(nrf_ctx* c, const float intr[4], const float* pose, bool to_host) {
-  static const bool threaded = std::getenv("NRF_NO_ENQUEUE_THREADS") == nullptr;
+  const bool threaded = std::getenv("NRF_NO_ENQUEUE_THREADS") == nullptr;
+  const char* from_env = std::getenv("NRF_ENQUEUE_THREADS_FROM");   // tests: exercise the threads on a 2-GPU box
+  const size_t threads_from = from_env ? (size_t)std::max(2, std::atoi(from_env)) : 4;
   // measured (profiles/r2_ab_enqueue_threads.json): 8 devices, synchronous per-frame call 967 -> 1 040 M rays/s, batch call
   // 1 103 -> 1 125 M; 2 devices 334 -> 331 / 342 -> 334 (the hand-off costs more than two devices' launches): from 4 devices up
-  if (c->devs.size() >= 4 && threaded) {
+  if (c->devs.size() >= threads_from && threaded) {
     if (c->workers.size() != c->devs.size()) start_workers(c);
     for (size_t g = 1; g < c->devs.size(); ++g) {
       DevWorker* w = c->workers[g].get();

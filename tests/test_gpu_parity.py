@@ -289,6 +289,33 @@ def test_two_gpus_batch_pipeline_no_tearing(pair):
         assert np.array_equal(dep[k].reshape(H, W), alone[k][1]), k
 
 
+def test_two_gpus_enqueue_threads(pair, monkeypatch):
+    """From four devices up every device beyond the first is enqueued by its own host thread; NRF_ENQUEUE_THREADS_FROM=2
+    switches that on for a two-device context.  Frames (synchronous, asynchronous, batch) must equal the single-GPU ones."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    monkeypatch.setenv("NRF_ENQUEUE_THREADS_FROM", "2")
+    name, sc, r, O = pair
+    W, H = 192, 128
+    intr = syn.intrinsics(W, H)
+    poses = np.stack([syn.look_at_pose(syn.camera_radius(name), 20.0, 50.0 * k) for k in range(5)])
+    r.set_shard(0, 1)
+    r.set_resolution((W, H))
+    alone = [r.render_frame(intr, p)[0].copy() for p in poses]
+    r2 = NerfRender(2)
+    r2.load_raw(sc.desc, sc.params, sc.grid, sc.aabb)
+    r2.set_resolution((W, H))
+    for k, p in enumerate(poses):
+        assert np.array_equal(r2.render_frame(intr, p)[0], alone[k]), k
+    for p in poses:
+        r2.render_frame_device(intr, p)
+    r2.synchronize()
+    out = r2.render_batch(intr, poses)
+    r2.close()
+    assert all(np.array_equal(out[k].reshape(H, W, 3), alone[k]) for k in range(len(poses)))
+
+
 def _small_grid_scene(bound, cascades, grid_size=32):
     d = syn.make_desc(14, bound, cascades, grid_size=grid_size)
     scene = "sphere" if cascades == 1 else "unbounded"
