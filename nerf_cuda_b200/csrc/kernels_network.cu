@@ -238,14 +238,15 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
   uint32_t e[8];
   if (mode == 1) {
     const uint32_t m = lv.size - 1u;
+    // (a ^ b ^ c) & m == (a & m) ^ (b & m) ^ (c & m): six masks + eight 3-input XORs instead of eight XORs + eight masks
     const uint32_t hy0 = g1 * 2654435761u, hy1 = hy0 + 2654435761u, hz0 = g2 * 805459861u, hz1 = hz0 + 805459861u;
-    const uint32_t yz[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
-    const uint32_t g0p = g0 + 1u;
+    const uint32_t my[2] = {hy0 & m, hy1 & m}, mz[2] = {hz0 & m, hz1 & m};
+    const uint32_t x0 = g0 & m, x1 = (g0 + 1u) & m;
     const bool odd = g0 & 1u;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      e[2 * j] = (g0 ^ yz[j]) & m;
-      e[2 * j + 1] = (g0p ^ yz[j]) & m;
+      e[2 * j] = x0 ^ my[j & 1] ^ mz[j >> 1];
+      e[2 * j + 1] = x1 ^ my[j & 1] ^ mz[j >> 1];
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -261,12 +262,12 @@ __device__ __forceinline__ void level_load(const LevelInfo& lv, float u0, float 
     // the host for the levels whose lanes share cache lines anyway (NRF_PAIR_FROM)
     const uint32_t m = lv.size - 1u;
     const uint32_t hy0 = g1 * 2654435761u, hy1 = hy0 + 2654435761u, hz0 = g2 * 805459861u, hz1 = hz0 + 805459861u;
-    const uint32_t yz[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
-    const uint32_t g0p = g0 + 1u;
+    const uint32_t my[2] = {hy0 & m, hy1 & m}, mz[2] = {hz0 & m, hz1 & m};
+    const uint32_t x0 = g0 & m, x1 = (g0 + 1u) & m;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      e[2 * j] = (g0 ^ yz[j]) & m;
-      e[2 * j + 1] = (g0p ^ yz[j]) & m;
+      e[2 * j] = x0 ^ my[j & 1] ^ mz[j >> 1];
+      e[2 * j + 1] = x1 ^ my[j & 1] ^ mz[j >> 1];
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) T.raw[k] = tab_ld32(tl + e[k]);
