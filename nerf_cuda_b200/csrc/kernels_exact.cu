@@ -105,6 +105,7 @@ struct RayCtx {
   uint32_t lut_a[3];  // shared-memory byte address of lut[1 - signbit(d_a)]: entry n + 1 (d >= +0) or n (sign set)
   float o[3], bound, dt_gamma, halfH, hm1, t_lo, t_hi, dt_min, dt_max;   // pinned copies of per-frame constants
   uint32_t H;
+  uint32_t rbh_base;    // FAST: bits(0.5*H) + bits(1.0): minus bits(2^level) it is bits(0.5*H * 2^-level)
   int cm1;
   const uint32_t* occ;  // P.occupancy, pinned like the constants above
 };
@@ -116,6 +117,7 @@ __device__ __forceinline__ void ray_ctx(const MarchParams& P, const float* lut, 
   R.t_lo = lds_f32(cb + 28); R.t_hi = lds_f32(cb + 32);
   R.H = __float_as_uint(lds_f32(cb + 36)); R.cm1 = (int)__float_as_uint(lds_f32(cb + 40));
   R.dt_min = lds_f32(cb + 44); R.dt_max = lds_f32(cb + 48);
+  R.rbh_base = __float_as_uint(R.halfH) + 0x3f800000u;
   R.occ = reinterpret_cast<const uint32_t*>(((unsigned long long)__float_as_uint(lds_f32(cb + 56)) << 32) |
                                             __float_as_uint(lds_f32(cb + 52)));
 #pragma unroll
@@ -169,9 +171,14 @@ __device__ __forceinline__ bool march_step(const MarchParams& P, const RayCtx& R
     ny = (int)(__float_as_uint(__fadd_rz(fminf(__fmaf_rn(y, mip_rbound, 1.0f) * halfH, hm1), 8388608.f)) & 0x7fffffu);
     nz = (int)(__float_as_uint(__fadd_rz(fminf(__fmaf_rn(z, mip_rbound, 1.0f) * halfH, hm1), 8388608.f)) & 0x7fffffu);
 #else
-    nx = (int)fminf(__fmaf_rn(x, mip_rbound, 1.0f) * halfH, hm1);
-    ny = (int)fminf(__fmaf_rn(y, mip_rbound, 1.0f) * halfH, hm1);
-    nz = (int)fminf(__fmaf_rn(z, mip_rbound, 1.0f) * halfH, hm1);
+    // RN(x*rb + 1) * (0.5*H) == RN(x*(rb*0.5*H) + 0.5*H): rb and 0.5*H are powers of two (FAST requires it), and scaling by a
+    // power of two commutes with rounding (no overflow / subnormals: the values lie in [0, H]) — one FFMA instead of FFMA+FMUL
+    uint32_t rbh_bits;
+    asm("sub.u32 %0, %1, %2;" : "=r"(rbh_bits) : "r"(R.rbh_base), "r"(__float_as_uint(pow2)));
+    const float rbh = __uint_as_float(rbh_bits);
+    nx = (int)fminf(__fmaf_rn(x, rbh, halfH), hm1);
+    ny = (int)fminf(__fmaf_rn(y, rbh, halfH), hm1);
+    nz = (int)fminf(__fmaf_rn(z, rbh, halfH), hm1);
 #endif
   } else {
     nx = (int)clampf(__fmaf_rn(x, mip_rbound, 1.0f) * halfH, 0.0f, hm1);   // reference SASS: FFMA(x, rb, 1), DMUL x2
