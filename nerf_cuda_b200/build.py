@@ -61,7 +61,9 @@ VARIANTS = {
     "evict": ["-DNRF_EXP_EVICT=1"],                    # table loads L2::evict_last, sample stream loads/stores evict_first
     "smem_l01": ["-DNRF_EXP_SMEM_L01=1"],              # dense levels 0-1 staged in shared memory (LDS instead of LDG)
     "floor_magic_evict": ["-DNRF_EXP_FLOOR_MAGIC=1", "-DNRF_EXP_EVICT=1"],
-    "march_magic": ["-DNRF_EXP_MARCH_MAGIC=1"],      # march step: F2I.TRUNC x3 (XU pipe) -> FADD.RZ + mantissa mask
+    "march_magic": ["-DNRF_EXP_MARCH_MAGIC=1"],
+    "tcache128": ["-DNRF_TCACHE=128"],                # 128 instead of 64 cached sample t's per ray (1 GB at 1080p)
+    "tcache32": ["-DNRF_TCACHE=32"],      # march step: F2I.TRUNC x3 (XU pipe) -> FADD.RZ + mantissa mask
 }
 
 

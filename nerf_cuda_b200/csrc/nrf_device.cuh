@@ -23,7 +23,9 @@
 #define NRF_L 16          // hash-grid levels (base.json)
 #define NRF_TILE 128      // samples per MMA tile == UMMA M
 #define NRF_MAX_STEPS_D 1024
+#ifndef NRF_TCACHE
 #define NRF_TCACHE 64     // sample t values cached per ray between the two march passes (kernels_exact.cu)
+#endif
 
 struct LevelInfo {
   uint32_t offset;  // first entry of the level (in entries)
