@@ -97,13 +97,18 @@ __device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, ui
 }
 // D[128 x N] = A[128 x K] (TMEM, K/2 columns from tmem_a) * W[n0 .. n0+N)[K]^T.  W is stored for NFULL rows in the K-major
 // core-matrix order (LBO = NFULL*16 between 8-element K chunks, SBO = 128 between 8-row groups).
+// w16 = (shared-memory address of the weight block) >> 4, computed once per kernel; byte_off = compile-time offset of the
+// matrix (+ row offset) inside the block.  The descriptor's low word is then ONE add per MMA — start address, in 16-byte
+// units, plus a constant that carries the leading-dimension field — and its high word a constant (the 20 KB block sits
+// far below 2^18, so the 14-bit address field never carries into the LBO field).
 template <int N, int K, int NFULL>
-__device__ __forceinline__ void issue_layer_ts(uint32_t tmem_d, uint32_t tmem_a, uint32_t w_addr, int n0) {
+__device__ __forceinline__ void issue_layer_ts(uint32_t tmem_d, uint32_t tmem_a, uint32_t w16, int byte_off) {
   constexpr uint32_t idesc = umma_idesc(NRF_TILE, N);
+  constexpr uint32_t hi = (uint32_t)(128 >> 4) | (1u << 14);   // SBO = 128 B at [32,46), version 1 at [46,48)
 #pragma unroll
   for (int kk = 0; kk < K / 16; ++kk) {
-    const uint64_t bd = umma_desc(w_addr + n0 * 16 + kk * 2 * (NFULL * 16), NFULL * 16, 128);
-    umma_f16_ts(tmem_d, tmem_a + kk * 8, bd, idesc, kk > 0);
+    const uint32_t lo = w16 + (uint32_t)((byte_off + kk * 2 * (NFULL * 16)) >> 4) + ((uint32_t)((NFULL * 16) >> 4) << 16);
+    umma_f16_ts(tmem_d, tmem_a + kk * 8, ((uint64_t)hi << 32) | lo, idesc, kk > 0);
   }
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
@@ -428,7 +433,10 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
   uint64_t* mbars = reinterpret_cast<uint64_t*>(smem + SMEM_W_BYTES);           // one per group
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SMEM_W_BYTES + 64);
 
-  const int tid = threadIdx.x, warp = tid >> 5, g = tid >> 7, gt = tid & 127;
+  // warp and group index read back from lane 0: the compiler then knows them (and the TMEM addresses derived from them) to
+  // be warp-uniform and keeps them in uniform registers — the tcgen05 instructions take uniform operands, and without this
+  // every MMA issue moved its addresses there with an ELECT / R2UR.BROADCAST retry loop
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), g = warp >> 2, gt = tid & 127;
   const int n_tiles = (n + NRF_TILE - 1) / NRF_TILE;
   // contiguous chunk of tiles per CTA, interleaved over its NET_GROUPS groups
   const int per_cta = (n_tiles + gridDim.x - 1) / gridDim.x;
@@ -473,16 +481,16 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     __syncthreads();
     tc_fence_after();
   }
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   const uint32_t t_a = tmem_base + (uint32_t)(g * 64);         // A operand columns (lane field 0: the MMA's view)
   const uint32_t t_d = t_a + 32;                                // accumulator columns
   const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;  // this warp's 32 TMEM lanes
-  const uint32_t w_addr = smem_u32(sW);
+  const uint32_t w16 = (smem_u32(sW) & 0x3FFFFu) >> 4;   // the weight block's address field of every UMMA descriptor
   const int bar_id = 1 + g;
 
 #define GROUP_SYNC() do { tc_fence_before(); bar_sync_group(bar_id); } while (0)
 #define ISSUE(N_, K_, NFULL_, OFF_, N0_) \
-  do { if (gt == 0) { tc_fence_after(); issue_layer_ts<N_, K_, NFULL_>(t_d, t_a, w_addr + (OFF_), (N0_)); umma_commit(bar); } } while (0)
+  do { if (gt == 0) { tc_fence_after(); issue_layer_ts<N_, K_, NFULL_>(t_d, t_a, w16, (OFF_) + (N0_) * 16); umma_commit(bar); } } while (0)
 #define MMA_WAIT() do { mbar_wait(bar, phase); phase ^= 1; tc_fence_after(); } while (0)
 
 #if NRF_EXP_SMEM_L01
