@@ -91,6 +91,24 @@ int nrf_render_batch_rgbd(nrf_ctx* ctx, const float intr[4], const float* poses_
  * cumulative per-ray sample boundaries of all rounds but the last (1..3 values, ascending, < NRF_MAX_STEPS). */
 int nrf_set_termination(nrf_ctx* ctx, int mode, const int* bounds, int n_bounds);
 
+/* nrf_eval_samples_noalloc — NO COUNTERPART IN THE REFERENCE.
+ * Evaluates n samples (hash-grid encode -> density + colour MLP) WITHOUT ANY ALLOCATION, for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the intermediate fp16 features
+ * (64 bytes per sample) go to a fixed file-scope device array inside the library instead of an allocated buffer.  That array
+ * (NRF_NOALLOC_MAX_SAMPLES x 64 B = 4 MB) is held by every GPU that loads the library until the process exits.
+ *   positions_dev : DEVICE pointer, n x float4 {u, v, w, ignored}, positions normalised to [0,1]^3, 16-byte aligned
+ *   dirs_dev      : DEVICE pointer, n x float4 {dx, dy, dz, ignored}, direction normalised to [0,1] (d*0.5+0.5), 16-byte aligned
+ *   out_dev       : DEVICE pointer, n x 4 fp16 {r, g, b, sigma} (8 bytes per sample), 8-byte aligned
+ * The caller owns all three.  The two kernels are enqueued on the context's stream (nrf_stream) of device 0 and the call
+ * returns without synchronising; it calls no cudaMalloc / cudaFree or allocating library routine (the first call on a device
+ * resolves the array's device address with cudaGetSymbolAddress).  n > NRF_NOALLOC_MAX_SAMPLES is rejected with NRF_EINVAL:
+ * split the batch.  Results equal nrf_probe_samples on the same inputs.  Every call in the process (any context on that GPU)
+ * shares the one array: it keeps the last call's contents (nothing needs clearing: a call overwrites the n entries it reads),
+ * and calls that overlap on the GPU — other streams, other contexts on the same device — race on it; calls on one context
+ * are ordered by its stream. */
+#define NRF_NOALLOC_MAX_SAMPLES 65536
+int nrf_eval_samples_noalloc(nrf_ctx* ctx, int n, const void* positions_dev, const void* dirs_dev, void* out_dev);
+
 /* Memory micro-benchmarks on device 0 (roofline denominators for the hash gather).  mode 0: coalesced
  * 16-byte streaming reads over a window split across the CTAs (window >> L2 => HBM read bandwidth); mode 2: every CTA
  * streams the WHOLE window (per-SM footprint = window, so the SM's own L1 cannot serve it: window <= L2 => L2->SM bandwidth);

@@ -330,6 +330,12 @@ class NerfRender:
         _check(self._l.nrf_probe_network(self._ctx, n, _p(enc_u16, C.c_uint16), _p(dirs01, C.c_float), _p(out, C.c_float), impl))
         return out
 
+    def eval_samples_noalloc(self, n, positions_dev, dirs_dev, out_dev):
+        """nrf_eval_samples_noalloc: DEVICE pointers (ints): n x float4 positions, n x float4 directions (both normalised to
+        [0,1]), n x 4 fp16 out {r,g,b,sigma}.  Allocates nothing; asynchronous on the context's stream (synchronize() after)."""
+        _check(self._l.nrf_eval_samples_noalloc(self._ctx, int(n), C.c_void_p(int(positions_dev)), C.c_void_p(int(dirs_dev)),
+                                                C.c_void_p(int(out_dev))))
+
     def probe_samples(self, positions01, dirs01):
         positions01, dirs01 = _f32(positions01), _f32(dirs01)
         n = positions01.shape[0]

@@ -19,6 +19,7 @@
 #include <thread>
 #include <cmath>
 #include <cstdarg>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -1482,6 +1483,54 @@ extern "C" int nrf_probe_samples(nrf_ctx* c, int n, const float* positions, cons
   CU(cudaStreamSynchronize(D.stream));
   unpack_out(h, out);
   p4.release(); d4.release(); o.release();
+  return NRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- no-allocation entry point
+// nrf_eval_samples_noalloc (include/nerf_b200_ext.h): the two-kernel form of the sample evaluation — k_network<0> writes the
+// fp16 hash-grid features of every sample (64 B) to scratch, k_network<1> runs the MLP from that scratch — with the scratch in
+// a file-scope device array instead of a cudaMalloc'ed buffer, for callers that must not allocate (CUDA graph capture, tight
+// serving loops).  Every GPU that loads the library holds the array (4 MB) until exit.  In host code the array's NAME is a
+// host-side stand-in, not a device address: its device address is taken once per device with cudaGetSymbolAddress (with that
+// device current) and that pointer is what the kernels get.
+static __device__ __align__(256) uint4 g_noalloc_enc[(size_t)NRF_NOALLOC_MAX_SAMPLES * 4];
+static uint4* g_noalloc_ptr[64] = {};   // device address of g_noalloc_enc per CUDA device ordinal
+static std::mutex g_noalloc_mutex;
+
+static int noalloc_scratch(int dev, uint4** out) {   // call with device `dev` current
+  if (dev < 0 || dev >= 64) return fail(NRF_EINVAL, "nrf_eval_samples_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> l(g_noalloc_mutex);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    CU(cudaGetSymbolAddress(&p, g_noalloc_enc));
+    if (!p) return fail(NRF_ECUDA, "cudaGetSymbolAddress returned a null address for the no-allocation scratch");
+    g_noalloc_ptr[dev] = static_cast<uint4*>(p);
+  }
+  *out = g_noalloc_ptr[dev];
+  return NRF_OK;
+}
+
+extern "C" int nrf_eval_samples_noalloc(nrf_ctx* c, int n, const void* positions_dev, const void* dirs_dev, void* out_dev) {
+  NEED_MODEL(c);
+  if (n < 0) return fail(NRF_EINVAL, "nrf_eval_samples_noalloc: n < 0");
+  if (n > NRF_NOALLOC_MAX_SAMPLES)
+    return fail(NRF_EINVAL, "nrf_eval_samples_noalloc: %d samples exceed the fixed scratch of %d (NRF_NOALLOC_MAX_SAMPLES); split the call",
+                n, NRF_NOALLOC_MAX_SAMPLES);
+  if (n == 0) return NRF_OK;
+  if (!positions_dev || !dirs_dev || !out_dev) return fail(NRF_EINVAL, "nrf_eval_samples_noalloc: null pointer");
+  if (((uintptr_t)positions_dev & 15) || ((uintptr_t)dirs_dev & 15) || ((uintptr_t)out_dev & 7))
+    return fail(NRF_EINVAL, "nrf_eval_samples_noalloc: positions / dirs must be 16-byte aligned, out 8-byte aligned");
+  Device& D = c->devs[0];
+  CU(cudaSetDevice(D.dev));
+  uint4* scratch = nullptr;
+  { int rc = noalloc_scratch(D.dev, &scratch); if (rc) return rc; }
+  const int grid = network_grid(c, D, n);
+  // stage 1 writes entries [0, n) of the scratch in full and stage 2 reads only those: nothing has to start at zero, and what
+  // an earlier call left beyond n is never read
+  CU(nrf_launch_network(0, grid, D.stream, &D.net, n, static_cast<const float4*>(positions_dev), nullptr, nullptr, nullptr, 1,
+                        scratch, nullptr, nullptr, nullptr, nullptr));
+  CU(nrf_launch_network(1, grid, D.stream, &D.net, n, nullptr, nullptr, static_cast<const float4*>(dirs_dev), nullptr, 1,
+                        scratch, static_cast<uint2*>(out_dev), nullptr, nullptr, nullptr));
   return NRF_OK;
 }
 
