@@ -62,6 +62,8 @@ VARIANTS = {
     "smem_l01": ["-DNRF_EXP_SMEM_L01=1"],              # dense levels 0-1 staged in shared memory (LDS instead of LDG)
     "floor_magic_evict": ["-DNRF_EXP_FLOOR_MAGIC=1", "-DNRF_EXP_EVICT=1"],
     "march_magic": ["-DNRF_EXP_MARCH_MAGIC=1"],
+    "no_tail_sync": ["-DNRF_NO_TAIL_SYNC=1"],        # k_network: drop the group barrier at the end of a tile
+    "arrive_sync": ["-DNRF_ARRIVE_SYNC=1"],          # k_network: group barriers as mbarrier arrive + wait by the issuing thread
     "tcache128": ["-DNRF_TCACHE=128"],                # 128 instead of 64 cached sample t's per ray (1 GB at 1080p)
     "tcache32": ["-DNRF_TCACHE=32"],      # march step: F2I.TRUNC x3 (XU pipe) -> FADD.RZ + mantissa mask
 }

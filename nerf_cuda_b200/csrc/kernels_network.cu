@@ -36,7 +36,7 @@
 
 #define NET_GROUPS_DEFAULT 8   // template default (stage probes MODE 0/1 run 8 groups x 128 threads); the frame path launches 7 (g_net_groups), 6 / 8 via NRF_NET_GROUPS
 #define SMEM_W_BYTES 20480
-#define NET_SMEM (SMEM_W_BYTES + 128)
+#define NET_SMEM (SMEM_W_BYTES + 256)   // weights | 8 MMA mbarriers | TMEM slot | (+128) 8 "operands ready" mbarriers
 #define NET_SMEM_L01 (66 * 1024)   // experiment NRF_EXP_SMEM_L01: room for the two coarsest (dense) levels behind the weights
 #ifdef NRF_EXP_SMEM_L01
 #if NRF_EXP_SMEM_L01
@@ -71,6 +71,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "@p bra DONE;\n\t"
       "bra WAIT_LOOP;\n\t"
       "DONE:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -183,6 +186,12 @@ struct LevelTaps {
 #endif
 #ifndef NRF_EXP_SMEM_L01
 #define NRF_EXP_SMEM_L01 0
+#endif
+#ifndef NRF_NO_TAIL_SYNC      // 1: no group barrier at the end of a tile (the next tile's first one already orders the TMEM reads)
+#define NRF_NO_TAIL_SYNC 0
+#endif
+#ifndef NRF_ARRIVE_SYNC       // 1: "operands ready" as mbarrier arrive (one lane per warp) + wait by the issuing thread only
+#define NRF_ARRIVE_SYNC 0
 #endif
 #if NRF_EXP_EVICT
 // table entries: keep in L2 (evict_last); sample records / outputs: streamed once (evict_first, no L1 allocation)
@@ -460,6 +469,10 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
 
   uint32_t phase = 0;
   const uint32_t bar = smem_u32(mbars + g);
+#if NRF_ARRIVE_SYNC
+  uint32_t rphase = 0;
+  const uint32_t rbar = smem_u32(smem + SMEM_W_BYTES + 128) + 8u * (uint32_t)g;
+#endif
   {
     // weights: 20 KB, already in UMMA core-matrix order -> straight copy
     const uint4* src = P.mlp_packed;
@@ -472,6 +485,9 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
     }
 #endif
     if (gt == 0) mbar_init(bar, 1);
+#if NRF_ARRIVE_SYNC
+    if (gt == 0) mbar_init(rbar, 4);   // one arrival per warp of the group
+#endif
     if (warp == 0) {
       asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)) : "memory");
       asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -488,9 +504,17 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
   const uint32_t w16 = (smem_u32(sW) & 0x3FFFFu) >> 4;   // the weight block's address field of every UMMA descriptor
   const int bar_id = 1 + g;
 
+#if NRF_ARRIVE_SYNC
+  // a warp whose TMEM stores / loads are done announces it and goes on (to its gather slice or to the MMA wait); only the
+  // issuing thread waits for all four warps.  Between two uses every warp passes an MMA wait, so the phases cannot overlap.
+#define GROUP_SYNC() do { tc_fence_before(); __syncwarp(); if ((tid & 31) == 0) mbar_arrive(rbar); } while (0)
+#define ISSUE(N_, K_, NFULL_, OFF_, N0_) \
+  do { if (gt == 0) { mbar_wait(rbar, rphase); tc_fence_after(); issue_layer_ts<N_, K_, NFULL_>(t_d, t_a, w16, (OFF_) + (N0_) * 16); umma_commit(bar); } rphase ^= 1; } while (0)
+#else
 #define GROUP_SYNC() do { tc_fence_before(); bar_sync_group(bar_id); } while (0)
 #define ISSUE(N_, K_, NFULL_, OFF_, N0_) \
   do { if (gt == 0) { tc_fence_after(); issue_layer_ts<N_, K_, NFULL_>(t_d, t_a, w16, (OFF_) + (N0_) * 16); umma_commit(bar); } } while (0)
+#endif
 #define MMA_WAIT() do { mbar_wait(bar, phase); phase ^= 1; tc_fence_after(); } while (0)
 
 #if NRF_EXP_SMEM_L01
@@ -619,8 +643,13 @@ k_network(const __grid_constant__ NetParams P, int n, const float4* __restrict__
         out_st(out + i, make_uint2(pack_h2(r, gg), pack_h2(b, sigma)));
       }
     }
+#if !NRF_NO_TAIL_SYNC && !NRF_ARRIVE_SYNC
     // the next tile's first tcgen05.st / MMA of this group must not overtake these TMEM reads
     GROUP_SYNC();
+#endif
+    // (without it: a warp's next tcgen05.st touches only its own 32 lanes of the A columns, which no MMA reads any more — the
+    // tile's last MMA was waited for above — and the next MMA is issued behind the next tile's first group barrier, which every
+    // warp reaches only after its tcgen05.wait::ld)
   }
 #undef GROUP_SYNC
 #undef ISSUE
