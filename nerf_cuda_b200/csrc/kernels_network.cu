@@ -31,6 +31,7 @@
 // the MLP accumulates in fp32 (TMEM) and rounds to fp16 at each layer boundary like the oracle (the reference
 // accumulates in fp16 inside wmma: outputs agree to ~5e-4 absolute, tests/test_ref_cuda_golden.py).
 #include <cstdlib>
+#include <mutex>
 
 #include "nrf_device.cuh"
 
@@ -741,16 +742,26 @@ static void net_attr() {
 }
 static bool g_specialise = true;   // NRF_NO_SPECIALISE=1: always the generic kernel (A/B, tests of the generic path at full size)
 static int g_net_groups = 7;   // measured on B200 (C3): 7 groups = 896 threads x 72 registers, no spills: 3-4 % faster than 8 x 64 (spills), 6 is slower again
+// Function attributes (shared-memory size, carveout preference) belong to the CURRENT device: set once per device, and safely
+// when several host threads enqueue the first frames of a multi-device context at the same time.
 static void nrf_network_setup() {
-  static bool attr_set = false;
-  if (attr_set) return;
-  net_attr<0, 8>(); net_attr<1, 8>(); net_attr<2, 8>(); net_attr<2, 7>(); net_attr<2, 6>(); net_attr<2, 7, NRF_LMODES_T19>(); net_attr<2, 7, NRF_LMODES_T19_B16>(); net_attr<2, 7, NRF_LMODES_T24>();
-  g_specialise = getenv("NRF_NO_SPECIALISE") == nullptr;
-  if (const char* e = getenv("NRF_NET_GROUPS")) {   // experiment: fewer groups = more registers per thread
-    const int g = atoi(e);
-    if (g == 6 || g == 7 || g == 8) g_net_groups = g;
+  static std::mutex m;
+  static bool attr_set[64] = {};
+  static bool env_read = false;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+  std::lock_guard<std::mutex> l(m);
+  if (!env_read) {
+    g_specialise = getenv("NRF_NO_SPECIALISE") == nullptr;
+    if (const char* e = getenv("NRF_NET_GROUPS")) {   // experiment: fewer groups = more registers per thread
+      const int g = atoi(e);
+      if (g == 6 || g == 7 || g == 8) g_net_groups = g;
+    }
+    env_read = true;
   }
-  attr_set = true;
+  if (attr_set[dev]) return;
+  net_attr<0, 8>(); net_attr<1, 8>(); net_attr<2, 8>(); net_attr<2, 7>(); net_attr<2, 6>(); net_attr<2, 7, NRF_LMODES_T19>(); net_attr<2, 7, NRF_LMODES_T19_B16>(); net_attr<2, 7, NRF_LMODES_T24>();
+  attr_set[dev] = true;
 }
 
 // grid = number of persistent CTAs (<= SM count); each walks a contiguous chunk of ceil(tiles/grid) tiles.
